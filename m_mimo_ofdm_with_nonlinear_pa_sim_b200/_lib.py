@@ -1,0 +1,99 @@
+"""ctypes binding of include/mmimo_b200.h.  Loading fails loudly: there is no CPU fallback."""
+import ctypes as C
+import os
+
+from . import _build
+
+c_f_p = C.POINTER(C.c_float)
+c_d_p = C.POINTER(C.c_double)
+c_u8_p = C.POINTER(C.c_uint8)
+c_u32_p = C.POINTER(C.c_uint32)
+c_u64_p = C.POINTER(C.c_uint64)
+
+
+class LinkConfig(C.Structure):
+    _fields_ = [("constel_size", C.c_int32), ("n_fft", C.c_int32), ("n_sub_carr", C.c_int32), ("n_ant", C.c_int32),
+                ("pa_kind", C.c_int32), ("channel_kind", C.c_int32), ("receiver_kind", C.c_int32),
+                ("skip_attenuation", C.c_int32), ("ibo_db", C.c_double), ("p_hardness", C.c_double),
+                ("center_freq", C.c_double), ("carrier_spacing", C.c_double), ("rx_pos", C.c_double * 3),
+                ("rx_loc_var", C.c_double), ("ant_gain_db", C.c_double), ("tx_pos", c_d_p), ("freqs", c_d_p)]
+
+
+class SimRequest(C.Structure):
+    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("incl_clean_run", C.c_int32), ("reserved", C.c_int32),
+                ("snr_db", C.c_double), ("csi_eps", C.c_double), ("seed", C.c_uint64), ("frame_id0", C.c_uint64),
+                ("rx_pos", c_d_p), ("h_true", c_f_p), ("h_loop", c_f_p), ("tx_idx", c_u8_p), ("noise", c_f_p),
+                ("clean_rx_pos", c_d_p), ("clean_h_true", c_f_p), ("clean_h_loop", c_f_p), ("clean_tx_idx", c_u8_p),
+                ("clean_noise", c_f_p)]
+
+
+class SimResult(C.Structure):
+    _fields_ = [("err", c_u64_p), ("clean_err", c_u64_p), ("bits_per_frame", C.c_uint64), ("det", c_u8_p),
+                ("err_per_frame", c_u32_p), ("rx_eq", c_f_p), ("corr", c_f_p), ("h_true", c_f_p), ("v", c_f_p),
+                ("agc", c_f_p), ("pa_p0", c_f_p), ("alpha", c_f_p), ("rx_pos", c_d_p), ("clean_det", c_u8_p)]
+
+
+class MmimoError(RuntimeError):
+    pass
+
+
+_LIB = None
+
+# every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = ["mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
+           "mmimo_configure", "mmimo_set_ibo", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
+           "mmimo_launch_count"]
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load(build_if_missing: bool = True):
+    """dlopen libmmimo_b200.so (building it in-tree with nvcc when absent or stale and nvcc exists)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = lib_path()
+    if build_if_missing and _build.is_stale():
+        try:
+            _build.build()
+        except Exception as exc:  # no nvcc on this box: a prebuilt .so is still fine
+            if not os.path.isfile(path):
+                raise MmimoError("libmmimo_b200.so is missing and could not be built: %s" % exc) from exc
+    if not os.path.isfile(path):
+        raise MmimoError("libmmimo_b200.so not found at %s - run `python __graft_entry__.py build`" % path)
+    lib = C.CDLL(path)
+    lib.mmimo_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    lib.mmimo_create.restype = C.c_int
+    lib.mmimo_destroy.argtypes = [C.c_void_p]
+    lib.mmimo_destroy.restype = None
+    lib.mmimo_last_error.restype = C.c_char_p
+    lib.mmimo_version.restype = C.c_char_p
+    lib.mmimo_stream.argtypes = [C.c_void_p]
+    lib.mmimo_stream.restype = C.c_void_p
+    lib.mmimo_synchronize.argtypes = [C.c_void_p]
+    lib.mmimo_configure.argtypes = [C.c_void_p, C.POINTER(LinkConfig)]
+    lib.mmimo_set_ibo.argtypes = [C.c_void_p, C.c_double]
+    lib.mmimo_link_simulate.argtypes = [C.c_void_p, C.POINTER(SimRequest), C.POINTER(SimResult)]
+    lib.mmimo_link_enqueue.argtypes = [C.c_void_p, C.POINTER(SimRequest)]
+    lib.mmimo_link_fetch.argtypes = [C.c_void_p, C.c_int32, c_u64_p, c_u64_p]
+    lib.mmimo_launch_count.argtypes = [C.c_void_p]
+    lib.mmimo_launch_count.restype = C.c_uint64
+    _bind_stage_ops(lib)
+    _LIB = lib
+    return lib
+
+
+def _bind_stage_ops(lib):
+    """argtypes of the stage-level entry points (filled in by _stage_abi when present)."""
+    try:
+        from . import _stage_abi
+    except ImportError:
+        return
+    _stage_abi.bind(lib)
+
+
+def check(lib, rc):
+    if rc != 0:
+        raise MmimoError(lib.mmimo_last_error().decode("utf-8", "replace"))

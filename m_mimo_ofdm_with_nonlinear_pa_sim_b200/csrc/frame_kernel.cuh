@@ -1,0 +1,191 @@
+// Fused Monte-Carlo frame kernel: one CTA (256 threads) runs whole frames
+//   bits -> QAM -> per-antenna precode -> IFFT -> PA -> FFT -> channel MAC over antennas -> AWGN -> AGC
+//   -> [detect -> count errors -> regenerate all antennas -> subtract distortion estimate] x (I+1)
+// i.e. the loop body of mp_model.py:208-222 with McncReceiver.receive (corrector.py:165-207) or
+// CncReceiver.receive (corrector.py:52-112) inlined.  The sum over antennas stays in registers: every
+// thread owns the same 8 data sub-carriers (native slot order, link_common.cuh) for every antenna.
+#pragma once
+#include "link_common.cuh"
+
+namespace mmimo {
+
+struct FrameScalars {   // written per frame by k_prep_realisation
+    float pa_p0_tx;     // PA parameter of the real transmission (sat. power or cubic coefficient)
+    float pa_p0_loop;   // PA parameter inside the receiver's regeneration loop
+    float noise_sigma;  // std of each real noise component on a data sub-carrier (noise.py:64-66)
+    float noise_sigma_clean;
+};
+
+struct FrameArgs {
+    // pass 0: the real transmission (antenna_array.py:58-140, channel.py:74-89)
+    const float2* h_true; long long h_true_fs;      // [F][k_tx][2048] native slots; frame stride in float2
+    const float2* v_tx;   long long v_tx_fs;        // [F][k_tx][2048], pre-scaled by 1/64
+    int k_tx;
+    // passes 1..I: the receiver's model of the transmitter
+    const float2* h_loop; long long h_loop_fs;      // MCNC: channel knowledge; CNC: ones, stride 0
+    const float2* v_loop; long long v_loop_fs;      // MCNC: == v_tx; CNC: 1/64, stride 0
+    int k_loop;
+    const float2* agc_inv_rx;   long long agc_rx_fs;    // 1/(64*agc) applied to pass 0 (mp_model.py:214)
+    const float2* agc_inv_loop; long long agc_loop_fs;  // 1/(64*agc_corr_vec) (corrector.py:200) or 1/(64*alpha)
+    const FrameScalars* scal;   long long scal_fs;      // per frame (stride 1) or shared (stride 0)
+    float pa_p1;                                     // Rapp hardness
+    int n_iter;                                      // I: detections 0..I are produced
+    Qam qam;
+    int n_frames;
+    // inputs: injected or generated (Philox)
+    const uint8_t* tx_idx;       // [F][2048] native slots, or nullptr
+    const float2* noise;         // [F][2048] native slots (added before the AGC), or nullptr
+    uint64_t seed; uint64_t frame_id0;
+    // outputs
+    uint8_t* det_out;            // [F][I+1][2048] native slots, or nullptr
+    float2* rx_eq_out;           // [F][2048] equalised received data sub-carriers, or nullptr
+    float2* corr_out;            // [F][I+1][2048] corrected symbols fed to the slicer, or nullptr
+    uint32_t* err_out;           // [F][I+1], or nullptr
+    unsigned long long* err_total;  // [I+1] accumulated with atomics
+};
+
+constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048 + 2048;
+constexpr int FRAME_SMEM_BYTES = FRAME_SMEM_FLOAT2 * 8 + 64 * 4;
+
+// One antenna: x (8 data slots, already precoded, 1/64 folded in) -> IFFT -> PA -> FFT; on return
+// x[0..3], x[12..15] hold the data bins of this thread (thread 0: x[4] = bin 1024).
+template <int PA>
+__device__ __forceinline__ void antenna_chain(float2 (&x)[16], float2* bufA, float2* bufB, const float2* tw2,
+                                              const Tw1& tw1, const int t, const float p0, const float sqrt_p0,
+                                              const float p1) {
+    fft4096<+1, true, false>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = pa_apply<PA>(x[j], p0, sqrt_p0, p1);
+    fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t);
+}
+
+template <int PA>
+__global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a, const float2* __restrict__ tw4096,
+                                                               const float2* __restrict__ tw256) {
+    extern __shared__ float2 smem[];
+    float2* bufA = smem;
+    float2* bufB = smem + 4096;
+    float2* tw2 = smem + 8192;
+    float2* sym_s = tw2 + 256;     // current symbols, thread-private addresses jp*256+t
+    float2* rxeq_s = sym_s + 2048;  // equalised received signal, thread-private addresses
+    unsigned int* err_s = reinterpret_cast<unsigned int*>(rxeq_s + 2048);
+
+    const int t = threadIdx.x;
+    tw2[t] = tw256[t];
+    if (t < 64) err_s[t] = 0;
+    Tw1 tw1;
+    load_tw1(tw1, tw4096, t);
+    __syncthreads();
+
+    for (int f = blockIdx.x; f < a.n_frames; f += gridDim.x) {
+        const FrameScalars sc = a.scal[f * a.scal_fs];
+        // ---- transmitted symbols -------------------------------------------------------------
+        uint32_t txw[2];
+        if (a.tx_idx) {
+            const uint8_t* p = a.tx_idx + (size_t)f * N_SC;
+            txw[0] = txw[1] = 0;
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
+        } else {
+            uint32_t r[4];
+            const uint64_t fid = a.frame_id0 + f;
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
+                          (uint32_t)(a.seed >> 32), r);
+            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+            txw[0] = r[0] & m4;
+            txw[1] = r[1] & m4;
+        }
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp)
+            sym_s[jp * 256 + t] = qam_symbol(a.qam, (txw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+
+        for (int pass = 0; pass <= a.n_iter; ++pass) {
+            const bool first = (pass == 0);
+            const int K = first ? a.k_tx : a.k_loop;
+            const float2* __restrict__ H = first ? a.h_true + f * a.h_true_fs : a.h_loop + f * a.h_loop_fs;
+            const float2* __restrict__ V = first ? a.v_tx + f * a.v_tx_fs : a.v_loop + f * a.v_loop_fs;
+            const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
+            const float sqrt_p0 = sqrtf(p0);
+            float2 acc[8];
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) acc[jp] = make_float2(0.f, 0.f);
+
+            for (int k = 0; k < K; ++k) {
+                const float2* __restrict__ vk = V + (size_t)k * N_SC;
+                const float2* __restrict__ hk = H + (size_t)k * N_SC;
+                float2 x[16];
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) x[jp_to_j(jp)] = cmul(sym_s[jp * 256 + t], __ldg(vk + jp * 256 + t));
+#pragma unroll
+                for (int j = 4; j < 12; ++j) x[j] = make_float2(0.f, 0.f);
+                if (t == 0) { x[4] = x[0]; x[0] = make_float2(0.f, 0.f); }
+                antenna_chain<PA>(x, bufA, bufB, tw2, tw1, t, p0, sqrt_p0, a.pa_p1);
+                if (t == 0) x[0] = x[4];
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) acc[jp] = cfma(__ldg(hk + jp * 256 + t), x[jp_to_j(jp)], acc[jp]);
+            }
+
+            // ---- end of pass: equalise / estimate distortion / slice / count --------------------
+            uint32_t detw[2] = {0u, 0u};
+            const float2* __restrict__ ai =
+                first ? a.agc_inv_rx + f * a.agc_rx_fs : a.agc_inv_loop + f * a.agc_loop_fs;
+            float2 nz[8];
+            if (first) {
+                if (a.noise) {
+#pragma unroll
+                    for (int jp = 0; jp < 8; ++jp) nz[jp] = a.noise[(size_t)f * N_SC + jp * 256 + t];
+                } else {
+                    const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        uint32_t r[4];
+                        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_NOISE, (uint32_t)(t * 4 + q),
+                                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+                        const float2 g0 = box_muller(r[0], r[1]), g1 = box_muller(r[2], r[3]);
+                        nz[2 * q] = make_float2(g0.x * sc.noise_sigma, g0.y * sc.noise_sigma);
+                        nz[2 * q + 1] = make_float2(g1.x * sc.noise_sigma, g1.y * sc.noise_sigma);
+                    }
+                }
+            }
+            unsigned int nerr = 0;
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const int p = jp * 256 + t;
+                float2 corr;
+                if (first) {
+                    const float2 r = make_float2(fmaf(64.f, nz[jp].x, acc[jp].x), fmaf(64.f, nz[jp].y, acc[jp].y));
+                    corr = cmul(r, ai[p]);
+                    rxeq_s[p] = corr;
+                    if (a.rx_eq_out) a.rx_eq_out[(size_t)f * N_SC + p] = corr;
+                } else {
+                    const float2 z = cmul(acc[jp], ai[p]);
+                    const float2 d = csub(z, sym_s[p]);  // distortion estimate, corrector.py:205
+                    corr = csub(rxeq_s[p], d);           // corrector.py:184
+                }
+                if (a.corr_out) a.corr_out[((size_t)f * (a.n_iter + 1) + pass) * N_SC + p] = corr;
+                const uint32_t idx = qam_detect(a.qam, corr);
+                sym_s[p] = qam_symbol(a.qam, idx);
+                detw[jp >> 2] |= idx << (8 * (jp & 3));
+            }
+            nerr = __popc(detw[0] ^ txw[0]) + __popc(detw[1] ^ txw[1]);
+            nerr = __reduce_add_sync(0xffffffffu, nerr);
+            if ((t & 31) == 0) atomicAdd(&err_s[pass], nerr);
+            if (a.det_out) {
+                uint8_t* dp = a.det_out + ((size_t)f * (a.n_iter + 1) + pass) * N_SC;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) dp[jp * 256 + t] = (uint8_t)((detw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+            }
+        }
+        __syncthreads();
+        if (t <= a.n_iter) {
+            const unsigned int e = err_s[t];
+            err_s[t] = 0;
+            if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
+            atomicAdd(&a.err_total[t], (unsigned long long)e);
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace mmimo

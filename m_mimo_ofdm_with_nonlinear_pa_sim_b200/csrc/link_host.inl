@@ -1,0 +1,292 @@
+// Host orchestration of Link.simulate (mp_model.py:89-222) - included by mmimo_b200.cu.
+
+static double calc_alpha_host(double ibo_db) {  // modulation.py:178-189
+    const double g = pow(10.0, ibo_db / 20.0);
+    return 1.0 - exp(-g * g) + (sqrt(M_PI) * g / 2.0) * erfc(g);
+}
+
+template <int PA>
+static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int grid) {
+    k_link_frame<PA><<<grid, FFT_THREADS, FRAME_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
+}
+
+// upload a host array of `rows` x 2048 elements in data-sub-carrier order into `dst` (native slots)
+template <class T>
+static int upload_native(mmimo_ctx* c, const T* host, T* dst, size_t rows) {
+    const size_t bytes = rows * N_SC * sizeof(T);
+    if (c->stage.reserve(bytes)) return 1;
+    CK(cudaMemcpyAsync(c->stage.p, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    k_to_native<T><<<nblk(rows * N_SC), 256, 0, c->stream>>>(c->stage.as<T>(), dst, rows);
+    c->launches++;
+    return 0;
+}
+template <class T>
+static int download_native(mmimo_ctx* c, const T* src, T* host, size_t rows) {
+    const size_t bytes = rows * N_SC * sizeof(T);
+    if (c->stage.reserve(bytes)) return 1;
+    k_from_native<T><<<nblk(rows * N_SC), 256, 0, c->stream>>>(src, c->stage.as<T>(), rows);
+    c->launches++;
+    CK(cudaMemcpyAsync(host, c->stage.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // stage is reused by the next transfer
+    return 0;
+}
+
+struct RealisationIn {
+    const double* rx_pos;
+    const float* h_true;
+    const float* h_loop;
+    uint32_t pos_stream, ray_stream, csi_stream;
+};
+
+// channel -> (CSI error) -> MRT precoder + AGC for frames [c0, c0+n) of the request
+static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const RealisationIn& in, size_t c0, int n,
+                           float2** h_true_out, float2** h_loop_out) {
+    const mmimo_link_config& cfg = c->cfg;
+    const int K = cfg.n_ant;
+    const size_t hN = (size_t)n * K * N_SC;
+    float2* h_true = c->h_true.as<float2>();
+    float2* h_loop = h_true;
+    if (in.h_true) {
+        if (upload_native<float2>(c, reinterpret_cast<const float2*>(in.h_true) + c0 * K * N_SC, h_true, (size_t)n * K)) return 1;
+    } else if (cfg.channel_kind == MMIMO_CHAN_LOS || cfg.channel_kind == MMIMO_CHAN_TWO_PATH) {
+        ChanArgs ca{};
+        ca.tx_pos = c->tx_pos.as<double>();
+        ca.rx_pos_in = nullptr;
+        if (in.rx_pos) {
+            CK(cudaMemcpyAsync(c->rx_pos.p, in.rx_pos + c0 * 3, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream));
+            ca.rx_pos_in = c->rx_pos.as<double>();
+        }
+        ca.rx_pos_out = in.rx_pos ? nullptr : c->rx_pos.as<double>();
+        ca.freq_slot = c->freq_slot.as<double>();
+        ca.rx0[0] = cfg.rx_pos[0]; ca.rx0[1] = cfg.rx_pos[1]; ca.rx0[2] = cfg.rx_pos[2];
+        ca.loc_var = cfg.rx_loc_var;
+        ca.gain_lin = sqrt(pow(10.0, cfg.ant_gain_db / 10.0));
+        ca.kind = cfg.channel_kind == MMIMO_CHAN_TWO_PATH ? 1 : 0;
+        ca.skip_attenuation = cfg.skip_attenuation;
+        ca.seed = rq->seed; ca.frame_id0 = rq->frame_id0 + c0;
+        ca.pos_stream = in.pos_stream;
+        ca.h_out = h_true; ca.n_ant = K;
+        k_gen_channel<<<dim3(K, n), 256, 0, c->stream>>>(ca);
+        c->launches++;
+    } else if (cfg.channel_kind == MMIMO_CHAN_RAYLEIGH) {
+        RayleighArgs ra{};
+        ra.tx_pos = c->tx_pos.as<double>();
+        ra.freq_slot = c->freq_slot.as<double>();
+        ra.rx0[0] = cfg.rx_pos[0]; ra.rx0[1] = cfg.rx_pos[1]; ra.rx0[2] = cfg.rx_pos[2];
+        ra.gain_lin = sqrt(pow(10.0, cfg.ant_gain_db / 10.0));
+        ra.skip_attenuation = cfg.skip_attenuation;
+        ra.seed = rq->seed; ra.frame_id0 = rq->frame_id0 + c0; ra.stream = in.ray_stream;
+        ra.h_out = h_true; ra.n_ant = K;
+        k_gen_rayleigh<<<dim3(K, n), 256, 0, c->stream>>>(ra);
+        c->launches++;
+    } else {
+        return fail("mmimo_link: channel_kind INJECTED needs h_true in the request");
+    }
+    if (in.h_loop) {
+        if (c->h_loop.reserve(hN * 8)) return 1;
+        h_loop = c->h_loop.as<float2>();
+        if (upload_native<float2>(c, reinterpret_cast<const float2*>(in.h_loop) + c0 * K * N_SC, h_loop, (size_t)n * K)) return 1;
+    } else if (rq->csi_eps > 0.0) {
+        if (c->h_loop.reserve(hN * 8)) return 1;
+        h_loop = c->h_loop.as<float2>();
+        CsiArgs xa{};
+        xa.h_in = h_true; xa.h_out = h_loop; xa.eps = (float)rq->csi_eps; xa.scale = (float)sqrt(1.0 - rq->csi_eps * rq->csi_eps);
+        xa.seed = rq->seed; xa.frame_id0 = rq->frame_id0 + c0; xa.stream = in.csi_stream; xa.n_ant = K;
+        k_csi_error<<<dim3(K, n), 256, 0, c->stream>>>(xa);
+        c->launches++;
+    }
+    PrepArgs pa{};
+    pa.h_loop = h_loop; pa.h_fs = (long long)K * N_SC;
+    pa.v_in = nullptr;
+    pa.v_out = c->v.as<float2>();
+    pa.agc_inv = c->agc_inv.as<float2>();
+    pa.hkvk_inv = c->hkvk_inv.as<float2>();
+    pa.scal = c->scal.as<FrameScalars>();
+    pa.alpha_out = c->alpha.as<float>();
+    pa.n_ant = K; pa.n_frames = n;
+    pa.pa_kind = cfg.pa_kind; pa.is_mcnc = cfg.receiver_kind == MMIMO_RX_MCNC;
+    pa.ibo_lin = pow(10.0, cfg.ibo_db / 10.0);
+    pa.avg_symbol_power = avg_symbol_power(cfg.constel_size);
+    pa.avg_sample_power = pa.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
+    pa.snr_lin = pow(10.0, rq->snr_db / 10.0);
+    k_prep_realisation<<<n, 256, 0, c->stream>>>(pa);
+    c->launches++;
+    *h_true_out = h_true;
+    *h_loop_out = h_loop;
+    return 0;
+}
+
+static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result* rs) {
+    if (!c || !rq) return fail("mmimo_link: NULL argument");
+    if (!c->configured) return fail("mmimo_link: context not configured (call mmimo_configure)");
+    if (rq->n_frames <= 0) return 0;
+    if (rq->n_iter < 0 || rq->n_iter > 62) return fail("mmimo_link: n_iter must be 0..62 (got %d)", rq->n_iter);
+    CK(cudaSetDevice(c->device));
+    const mmimo_link_config& cfg = c->cfg;
+    const int K = cfg.n_ant, I = rq->n_iter;
+    const bool mcnc = cfg.receiver_kind == MMIMO_RX_MCNC;
+    const bool sep_loop = rq->h_loop || rq->clean_h_loop || rq->csi_eps > 0.0;
+    const bool want_det = rs && rs->det, want_corr = rs && rs->corr, want_rxeq = rs && rs->rx_eq;
+    // chunking: per-frame scratch bytes
+    size_t per_frame = (size_t)K * N_SC * 8 * (sep_loop ? 3 : 2) + (size_t)N_SC * (8 * 4 + 1) + 64 + (size_t)K * 4;
+    if (want_det) per_frame += (size_t)(I + 1) * N_SC;
+    if (want_corr) per_frame += (size_t)(I + 1) * N_SC * 8;
+    size_t chunk = std::max<size_t>(1, c->scratch_budget / per_frame);
+    chunk = std::min<size_t>(chunk, (size_t)rq->n_frames);
+    chunk = std::min<size_t>(chunk, 8192);
+    const size_t hB = chunk * K * N_SC * 8;
+    if (c->h_true.reserve(hB) || c->v.reserve(hB) || c->agc_inv.reserve(chunk * N_SC * 8) ||
+        c->hkvk_inv.reserve(chunk * N_SC * 8) || c->scal.reserve(chunk * sizeof(FrameScalars)) ||
+        c->alpha.reserve(chunk * K * 4) || c->rx_pos.reserve(chunk * 24) || c->tx_idx.reserve(chunk * N_SC) ||
+        c->noise.reserve(chunk * N_SC * 8) || c->err.reserve(chunk * (I + 1) * 4) || c->rx_eq.reserve(chunk * N_SC * 8))
+        return 1;
+    if (want_det && c->det.reserve(chunk * (I + 1) * N_SC)) return 1;
+    if (want_corr && c->corr.reserve(chunk * (I + 1) * N_SC * 8)) return 1;
+    if (!mcnc) {
+        if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 8) || c->cnc_agc_inv.reserve(N_SC * 8)) return 1;
+        const double alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
+        k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_ones.as<float2>(), make_float2(1.f, 0.f), N_SC);
+        k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float2>(), make_float2(1.f / 64.f, 0.f), N_SC);
+        k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_agc_inv.as<float2>(), make_float2((float)(1.0 / (64.0 * alpha)), 0.f), N_SC);
+        c->launches += 3;
+    }
+    unsigned long long* counters = c->counters.as<unsigned long long>();
+
+    for (size_t c0 = 0; c0 < (size_t)rq->n_frames; c0 += chunk) {
+        const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
+        float2 *h_true = nullptr, *h_loop = nullptr;
+        if (rq->incl_clean_run) {
+            RealisationIn in{rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
+            if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop)) return 1;
+            CleanArgs ca{};
+            ca.h_true = h_true; ca.h_fs = (long long)K * N_SC;
+            ca.v = c->v.as<float2>(); ca.v_fs = (long long)K * N_SC;
+            ca.hkvk_inv = c->hkvk_inv.as<float2>();
+            ca.scal = c->scal.as<FrameScalars>();
+            ca.n_ant = K; ca.n_frames = n;
+            ca.qam.log2side = log2_side(cfg.constel_size);
+            ca.tx_idx = nullptr; ca.noise = nullptr;
+            if (rq->clean_tx_idx) {
+                if (upload_native<uint8_t>(c, rq->clean_tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;
+                ca.tx_idx = c->tx_idx.as<uint8_t>();
+            }
+            if (rq->clean_noise) {
+                if (upload_native<float2>(c, reinterpret_cast<const float2*>(rq->clean_noise) + c0 * N_SC, c->noise.as<float2>(), n)) return 1;
+                ca.noise = c->noise.as<float2>();
+            }
+            ca.seed = rq->seed; ca.frame_id0 = rq->frame_id0 + c0;
+            ca.det_out = (rs && rs->clean_det) ? c->det.as<uint8_t>() : nullptr;
+            if (ca.det_out && c->det.reserve((size_t)chunk * (I + 1) * N_SC)) return 1;
+            ca.det_out = (rs && rs->clean_det) ? c->det.as<uint8_t>() : nullptr;
+            ca.err_out = nullptr;
+            ca.err_total = counters + 64;
+            k_clean_frame<<<n, 256, 0, c->stream>>>(ca);
+            c->launches++;
+            if (rs && rs->clean_det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->clean_det + c0 * N_SC, n)) return 1;
+        }
+        RealisationIn in{rq->rx_pos, rq->h_true, rq->h_loop, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
+        if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop)) return 1;
+
+        FrameArgs fa{};
+        fa.h_true = h_true; fa.h_true_fs = (long long)K * N_SC;
+        fa.v_tx = c->v.as<float2>(); fa.v_tx_fs = (long long)K * N_SC;
+        fa.k_tx = K;
+        fa.agc_inv_rx = c->agc_inv.as<float2>(); fa.agc_rx_fs = N_SC;
+        if (mcnc) {
+            fa.h_loop = h_loop; fa.h_loop_fs = (long long)K * N_SC;
+            fa.v_loop = fa.v_tx; fa.v_loop_fs = fa.v_tx_fs;
+            fa.k_loop = K;
+            fa.agc_inv_loop = fa.agc_inv_rx; fa.agc_loop_fs = N_SC;
+        } else {
+            fa.h_loop = c->cnc_ones.as<float2>(); fa.h_loop_fs = 0;
+            fa.v_loop = c->cnc_v.as<float2>(); fa.v_loop_fs = 0;
+            fa.k_loop = 1;
+            fa.agc_inv_loop = c->cnc_agc_inv.as<float2>(); fa.agc_loop_fs = 0;
+        }
+        fa.scal = c->scal.as<FrameScalars>(); fa.scal_fs = 1;
+        fa.pa_p1 = (float)cfg.p_hardness;
+        fa.n_iter = I;
+        fa.qam.log2side = log2_side(cfg.constel_size);
+        fa.n_frames = n;
+        fa.tx_idx = nullptr; fa.noise = nullptr;
+        if (rq->tx_idx) {
+            if (upload_native<uint8_t>(c, rq->tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;
+            fa.tx_idx = c->tx_idx.as<uint8_t>();
+        }
+        if (rq->noise) {
+            if (upload_native<float2>(c, reinterpret_cast<const float2*>(rq->noise) + c0 * N_SC, c->noise.as<float2>(), n)) return 1;
+            fa.noise = c->noise.as<float2>();
+        }
+        fa.seed = rq->seed; fa.frame_id0 = rq->frame_id0 + c0;
+        fa.det_out = want_det ? c->det.as<uint8_t>() : nullptr;
+        fa.rx_eq_out = want_rxeq ? c->rx_eq.as<float2>() : nullptr;
+        fa.corr_out = want_corr ? c->corr.as<float2>() : nullptr;
+        fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
+        fa.err_total = counters;
+        const int grid = std::min(n, 2 * c->n_sm);
+        switch (cfg.pa_kind) {
+            case MMIMO_PA_NONE: launch_frame<PA_NONE>(fa, c, grid); break;
+            case MMIMO_PA_SOFT_LIMITER: launch_frame<PA_SOFT_LIMITER>(fa, c, grid); break;
+            case MMIMO_PA_RAPP: launch_frame<PA_RAPP>(fa, c, grid); break;
+            default: launch_frame<PA_TOI>(fa, c, grid); break;
+        }
+        c->launches++;
+        CK(cudaGetLastError());
+
+        if (rs) {  // optional per-frame dumps
+            if (rs->det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->det + c0 * (I + 1) * N_SC, (size_t)n * (I + 1))) return 1;
+            if (rs->corr && download_native<float2>(c, c->corr.as<float2>(), reinterpret_cast<float2*>(rs->corr) + c0 * (I + 1) * N_SC, (size_t)n * (I + 1))) return 1;
+            if (rs->rx_eq && download_native<float2>(c, c->rx_eq.as<float2>(), reinterpret_cast<float2*>(rs->rx_eq) + c0 * N_SC, n)) return 1;
+            if (rs->h_true && download_native<float2>(c, h_true, reinterpret_cast<float2*>(rs->h_true) + c0 * K * N_SC, (size_t)n * K)) return 1;
+            if (rs->v) {
+                if (c->s_a.reserve((size_t)n * K * N_SC * 8)) return 1;
+                CK(cudaMemcpyAsync(c->s_a.p, c->v.p, (size_t)n * K * N_SC * 8, cudaMemcpyDeviceToDevice, c->stream));
+                k_scale<<<nblk((size_t)n * K * N_SC), 256, 0, c->stream>>>(c->s_a.as<float2>(), 64.f, (size_t)n * K * N_SC);
+                c->launches++;
+                if (download_native<float2>(c, c->s_a.as<float2>(), reinterpret_cast<float2*>(rs->v) + c0 * K * N_SC, (size_t)n * K)) return 1;
+            }
+            if (rs->agc) {
+                if (c->s_a.reserve((size_t)n * N_SC * 8)) return 1;
+                k_agc_from_inv<<<nblk((size_t)n * N_SC), 256, 0, c->stream>>>(c->agc_inv.as<float2>(), c->s_a.as<float2>(), (size_t)n * N_SC);
+                c->launches++;
+                if (download_native<float2>(c, c->s_a.as<float2>(), reinterpret_cast<float2*>(rs->agc) + c0 * N_SC, n)) return 1;
+            }
+            if (rs->err_per_frame) CK(cudaMemcpyAsync(rs->err_per_frame + c0 * (I + 1), c->err.p, (size_t)n * (I + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+            if (rs->alpha) CK(cudaMemcpyAsync(rs->alpha + c0 * K, c->alpha.p, (size_t)n * K * 4, cudaMemcpyDeviceToHost, c->stream));
+            if (rs->rx_pos && !rq->rx_pos && (cfg.channel_kind == MMIMO_CHAN_LOS || cfg.channel_kind == MMIMO_CHAN_TWO_PATH) && !rq->h_true)
+                CK(cudaMemcpyAsync(rs->rx_pos + c0 * 3, c->rx_pos.p, (size_t)n * 24, cudaMemcpyDeviceToHost, c->stream));
+            if (rs->pa_p0) {
+                std::vector<FrameScalars> sc(n);
+                CK(cudaMemcpyAsync(sc.data(), c->scal.p, (size_t)n * sizeof(FrameScalars), cudaMemcpyDeviceToHost, c->stream));
+                CK(cudaStreamSynchronize(c->stream));
+                for (int i = 0; i < n; ++i) rs->pa_p0[c0 + i] = sc[i].pa_p0_tx;
+            }
+        }
+    }
+    return 0;
+}
+
+extern "C" int mmimo_link_fetch(mmimo_ctx* c, int32_t n_iter, uint64_t* err, uint64_t* clean_err) {
+    if (!c) return fail("NULL context");
+    if (n_iter < 0 || n_iter > 62) return fail("mmimo_link_fetch: n_iter must be 0..62");
+    CK(cudaSetDevice(c->device));
+    unsigned long long h[65];
+    CK(cudaMemcpyAsync(h, c->counters.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemsetAsync(c->counters.p, 0, sizeof h, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (err) for (int i = 0; i <= n_iter; ++i) err[i] = h[i];
+    if (clean_err) clean_err[0] = h[64];
+    return 0;
+}
+
+extern "C" int mmimo_link_enqueue(mmimo_ctx* c, const mmimo_sim_request* rq) { return run_link(c, rq, nullptr); }
+
+extern "C" int mmimo_link_simulate(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result* rs) {
+    if (!rs || !rs->err) return fail("mmimo_link_simulate: result.err is required");
+    if (rq && rq->incl_clean_run && !rs->clean_err) return fail("mmimo_link_simulate: result.clean_err is required with incl_clean_run");
+    // counters accumulated by earlier enqueue calls must not leak into this result
+    if (c) { CK(cudaSetDevice(c->device)); CK(cudaMemsetAsync(c->counters.p, 0, 65 * 8, c->stream)); }
+    if (run_link(c, rq, rs)) return 1;
+    rs->bits_per_frame = (uint64_t)(2 * log2_side(c->cfg.constel_size)) * N_SC;
+    return mmimo_link_fetch(c, rq->n_iter, rs->err, rs->clean_err);
+}

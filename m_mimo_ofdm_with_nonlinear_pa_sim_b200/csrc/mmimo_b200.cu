@@ -1,0 +1,218 @@
+// libmmimo_b200.so - C ABI (include/mmimo_b200.h) over the sm_100a link kernels.
+// Host side only orchestrates: uploads, launches, downloads.  There is no CPU compute path.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/mmimo_b200.h"
+#include "prep_kernels.cuh"
+#include "stage_kernels.cuh"
+
+using namespace mmimo;
+
+static thread_local std::string g_err;
+
+static int fail(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CK(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// growable device buffer owned by the context
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) return fail("cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+        cap = bytes;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct mmimo_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool configured = false;
+    mmimo_link_config cfg{};
+    std::vector<double> tx_pos_h, freqs_h;
+    uint64_t launches = 0;
+    int n_sm = 148;
+    size_t scratch_budget = (size_t)12 << 30;
+    // tables
+    DevBuf tw4096, tw256, freq_slot, freq_bin, tx_pos;
+    // per-chunk scratch
+    DevBuf h_true, h_loop, v, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
+    DevBuf cnc_ones, cnc_v, cnc_agc_inv;
+    DevBuf counters;  // [0..63] distorted iterations, [64] clean
+    // stage-op scratch
+    DevBuf s_a, s_b, s_c, s_d;
+};
+
+template <class T>
+__global__ void k_to_native(const T* __restrict__ src, T* __restrict__ dst, size_t rows) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * N_SC) return;
+    const size_t r = i / N_SC;
+    const int p = (int)(i % N_SC);
+    dst[i] = src[r * N_SC + slot_to_sc(p)];
+}
+template <class T>
+__global__ void k_from_native(const T* __restrict__ src, T* __restrict__ dst, size_t rows) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * N_SC) return;
+    const size_t r = i / N_SC;
+    const int s = (int)(i % N_SC);
+    dst[i] = src[r * N_SC + sc_to_slot(s)];
+}
+// 1/z -> z for the AGC dump (agc_inv holds 1/(64 agc))
+__global__ void k_agc_from_inv(const float2* __restrict__ inv, float2* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float2 z = inv[i];
+    const double m = ((double)z.x * z.x + (double)z.y * z.y) * 64.0;
+    out[i] = make_float2((float)(z.x / m), (float)(-z.y / m));
+}
+__global__ void k_scale(float2* __restrict__ x, float s, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { x[i].x *= s; x[i].y *= s; }
+}
+__global__ void k_fill_c(float2* __restrict__ x, float2 v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] = v;
+}
+
+static inline unsigned nblk(size_t n, int bs = 256) { return (unsigned)((n + bs - 1) / bs); }
+
+extern "C" const char* mmimo_last_error(void) { return g_err.c_str(); }
+extern "C" const char* mmimo_version(void) { return "mmimo_b200 0.1 (sm_100a)"; }
+
+extern "C" int mmimo_create(mmimo_ctx** out, int device) {
+    if (!out) return fail("mmimo_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    CK(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail("mmimo_create: device %d not present (%d CUDA devices)", device, n);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail("mmimo_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    mmimo_ctx* c = new mmimo_ctx();
+    c->device = device;
+    c->n_sm = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    // twiddle tables, computed in double (forward sign)
+    std::vector<float2> t4(4096), t2(256);
+    for (int i = 0; i < 4096; ++i) {
+        const double a = -2.0 * M_PI * (double)i / 4096.0;
+        t4[i] = make_float2((float)cos(a), (float)sin(a));
+    }
+    for (int k1 = 0; k1 < 16; ++k1)
+        for (int n0 = 0; n0 < 16; ++n0) {
+            const double a = -2.0 * M_PI * (double)(k1 * n0) / 256.0;
+            t2[k1 * 16 + n0] = make_float2((float)cos(a), (float)sin(a));
+        }
+    if (c->tw4096.reserve(4096 * 8) || c->tw256.reserve(256 * 8) || c->counters.reserve(65 * 8)) { delete c; return 1; }
+    CK(cudaMemcpy(c->tw4096.p, t4.data(), 4096 * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->tw256.p, t2.data(), 256 * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemset(c->counters.p, 0, 65 * 8));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
+    if (stage_kernels_init()) { delete c; return 1; }
+    *out = c;
+    return 0;
+}
+
+extern "C" void mmimo_destroy(mmimo_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->v, &c->agc_inv,
+                     &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
+                     &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
+                     &c->s_a, &c->s_b, &c->s_c, &c->s_d};
+    for (DevBuf* b : all) b->release();
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" void* mmimo_stream(mmimo_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" uint64_t mmimo_launch_count(mmimo_ctx* c) { return c ? c->launches : 0; }
+extern "C" int mmimo_synchronize(mmimo_ctx* c) {
+    if (!c) return fail("NULL context");
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+static int log2_side(int constel) {
+    switch (constel) {
+        case 4: return 1;
+        case 16: return 2;
+        case 64: return 3;
+        case 256: return 4;
+    }
+    return -1;
+}
+
+static double avg_symbol_power(int constel) {  // mean |c|^2 of square QAM with levels +-1, +-3, ...: 2 (M-1) / 3
+    return 2.0 * (constel - 1) / 3.0;
+}
+
+extern "C" int mmimo_configure(mmimo_ctx* c, const mmimo_link_config* cfg) {
+    if (!c || !cfg) return fail("mmimo_configure: NULL argument");
+    if (cfg->n_fft != 4096 || cfg->n_sub_carr != 2048)
+        return fail("mmimo_configure: only n_fft=4096 / n_sub_carr=2048 is built (got %d / %d)", cfg->n_fft, cfg->n_sub_carr);
+    if (log2_side(cfg->constel_size) < 0)
+        return fail("Constellation size must be a power of some number, only square QAM supported. (got %d)", cfg->constel_size);
+    if (cfg->n_ant < 1 || cfg->n_ant > MAX_ANT) return fail("mmimo_configure: n_ant must be 1..%d (got %d)", MAX_ANT, cfg->n_ant);
+    if (cfg->pa_kind < 0 || cfg->pa_kind > 3) return fail("mmimo_configure: unknown pa_kind %d", cfg->pa_kind);
+    if (cfg->channel_kind < 0 || cfg->channel_kind > 3) return fail("mmimo_configure: unknown channel_kind %d", cfg->channel_kind);
+    if (!cfg->tx_pos || !cfg->freqs) return fail("mmimo_configure: tx_pos and freqs are required");
+    CK(cudaSetDevice(c->device));
+    c->cfg = *cfg;
+    c->tx_pos_h.assign(cfg->tx_pos, cfg->tx_pos + 3 * cfg->n_ant);
+    c->freqs_h.assign(cfg->freqs, cfg->freqs + cfg->n_fft);
+    c->cfg.tx_pos = c->tx_pos_h.data();
+    c->cfg.freqs = c->freqs_h.data();
+    std::vector<double> fs(N_SC);
+    for (int p = 0; p < N_SC; ++p) fs[p] = c->freqs_h[slot_to_bin(p)];
+    if (c->freq_slot.reserve(N_SC * 8) || c->freq_bin.reserve(4096 * 8) || c->tx_pos.reserve((size_t)cfg->n_ant * 24)) return 1;
+    CK(cudaMemcpyAsync(c->freq_slot.p, fs.data(), N_SC * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->freq_bin.p, c->freqs_h.data(), 4096 * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->tx_pos.p, c->tx_pos_h.data(), (size_t)cfg->n_ant * 24, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->configured = true;
+    return 0;
+}
+
+extern "C" int mmimo_set_ibo(mmimo_ctx* c, double ibo_db) {
+    if (!c || !c->configured) return fail("mmimo_set_ibo: context not configured");
+    c->cfg.ibo_db = ibo_db;
+    return 0;
+}
+
+#include "link_host.inl"
+#include "stage_host.inl"

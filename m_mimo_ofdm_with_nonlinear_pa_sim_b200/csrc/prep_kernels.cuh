@@ -1,0 +1,375 @@
+// Per-realisation kernels: channel generation, MRT precoder + AGC / alpha / noise bookkeeping,
+// and the FFT-free "no distortion" frame.  All per-sub-carrier arrays use the native slot order.
+#pragma once
+#include "frame_kernel.cuh"
+
+namespace mmimo {
+
+constexpr double C_LIGHT = 299792458.0;  // scipy.constants.c (channel.py:61,66)
+constexpr int MAX_ANT = 256;
+
+// uniform double in (0,1) from two 32-bit words
+__device__ __forceinline__ double u01(uint32_t hi, uint32_t lo) {
+    return ((double)hi * 4294967296.0 + (double)lo + 0.5) * (1.0 / 18446744073709551616.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_gen_channel: MisoLosFd / MisoTwoPathFd.calc_channel_mat (channel.py:35-72, :116-167) on the data
+// sub-carriers only; receiver position injected or drawn as in mp_model.py:143-148 (both offsets are
+// added to rx_loc_x - the reference's cord_y quirk).  grid = (K, F), block = 256.
+// ---------------------------------------------------------------------------------------------
+struct ChanArgs {
+    const double* tx_pos;     // [K][3]
+    const double* rx_pos_in;  // [F][3] or nullptr -> Philox
+    double* rx_pos_out;       // [F][3] or nullptr
+    const double* freq_slot;  // [2048] sub-carrier frequency per native slot (float32-rounded values, channel.py:51-52)
+    double rx0[3];            // nominal receiver position
+    double loc_var;           // rx_loc_var
+    double gain_lin;          // sqrt(10^((G_tx+G_rx)/10))
+    int kind;                 // 0 LOS, 1 two-path
+    int skip_attenuation;
+    uint64_t seed, frame_id0;
+    uint32_t pos_stream;      // RNG_POS or a clean-run stream
+    float2* h_out;            // [F][K][2048]
+    int n_ant;
+};
+
+__device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bool skip_att) {
+    const double x = d * f * (1.0 / C_LIGHT);
+    const float r = (float)(x - rint(x));
+    float s, c;
+    sincospif(2.0f * r, &s, &c);
+    if (skip_att) return make_float2(c, s);
+    const float a = (float)(gain * C_LIGHT / (4.0 * 3.14159265358979323846 * d * f));
+    return make_float2(a * c, a * s);
+}
+
+__global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
+    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
+    double rx[3];
+    if (a.rx_pos_in) {
+        rx[0] = a.rx_pos_in[f * 3 + 0]; rx[1] = a.rx_pos_in[f * 3 + 1]; rx[2] = a.rx_pos_in[f * 3 + 2];
+    } else {
+        uint32_t r[4];
+        const uint64_t fid = a.frame_id0 + f;
+        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.pos_stream, 0u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+        rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+        rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
+        rx[2] = a.rx0[2];
+    }
+    if (a.rx_pos_out && k == 0 && t < 3) a.rx_pos_out[f * 3 + t] = rx[t];
+    const double dx = a.tx_pos[k * 3 + 0] - rx[0], dy = a.tx_pos[k * 3 + 1] - rx[1], dz = a.tx_pos[k * 3 + 2] - rx[2];
+    const double d1 = sqrt(dx * dx + dy * dy + dz * dz);
+    double d2 = 0.0;
+    if (a.kind == 1) {
+        const double dxy = sqrt(dx * dx + dy * dy);
+        const double el = atan((a.tx_pos[k * 3 + 2] + rx[2]) / dxy);
+        const double sn = sin(el);
+        d2 = a.tx_pos[k * 3 + 2] / sn + rx[2] / sn;
+    }
+    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        const int p = jp * 256 + t;
+        const double fr = a.freq_slot[p];
+        float2 h = path_coeff(d1, fr, a.gain_lin, a.skip_attenuation);
+        if (a.kind == 1) {
+            const float2 g = path_coeff(d2, fr, a.gain_lin, a.skip_attenuation);
+            h.x -= g.x; h.y -= g.y;
+        }
+        out[p] = h;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_prep_realisation: AntennaArray.set_precoding_matrix(MRT) (antenna_array.py:163-171),
+// AntennaArray.update_distortion (:313-360) and Link.recalculate_agc (mp_model.py:290-329) for one
+// channel realisation per CTA.
+// ---------------------------------------------------------------------------------------------
+struct PrepArgs {
+    const float2* h_loop; long long h_fs;  // channel knowledge [F][K][2048]
+    const float2* v_in;                    // optional externally supplied precoder [F][K][2048] (unscaled)
+    float2* v_out;                         // [F][K][2048] precoder / 64
+    float2* agc_inv;                       // [F][2048]  1 / (64 * sum_k alpha_k h_k v_k)
+    float2* hkvk_inv;                      // [F][2048]  1 / (sum_k h_k v_k)        (clean run, no FFT scale)
+    FrameScalars* scal;                    // [F]
+    float* alpha_out;                      // [F][K] or nullptr
+    int n_ant, n_frames;
+    int pa_kind, is_mcnc;
+    double ibo_lin;            // 10^(ibo_db/10)  (TOI: 10^(toi_db/10))
+    double avg_symbol_power;   // 42 for 64-QAM (modulation.py:218)
+    double avg_sample_power;   // avg_symbol_power * n_sub_carr / n_fft (modulation.py:424)
+    double snr_lin;            // 10^(snr_db/10)
+};
+
+__device__ __forceinline__ double block_sum_256(double v, double* red_s, int t) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((t & 31) == 0) red_s[t >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red_s[w];
+    return s;
+}
+
+__global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
+    __shared__ float part_s[MAX_ANT][8];
+    __shared__ float alpha_s[MAX_ANT];
+    __shared__ double vkpow_s[MAX_ANT];
+    __shared__ double red_s[8];
+    const int f = blockIdx.x, t = threadIdx.x, K = a.n_ant;
+    const float2* __restrict__ H = a.h_loop + f * a.h_fs;
+    const float2* __restrict__ Vin = a.v_in ? a.v_in + (size_t)f * K * N_SC : nullptr;
+    float2* Vout = a.v_out + (size_t)f * K * N_SC;
+
+    float ninv[8];
+    if (!Vin) {
+        float nrm[8];
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) nrm[jp] = 0.f;
+        for (int k = 0; k < K; ++k) {
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const float2 h = H[(size_t)k * N_SC + jp * 256 + t];
+                nrm[jp] = fmaf(h.x, h.x, fmaf(h.y, h.y, nrm[jp]));
+            }
+        }
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) ninv[jp] = 1.0f / sqrtf(nrm[jp]);
+    }
+    // precoder out + per-antenna power
+    for (int k = 0; k < K; ++k) {
+        float pw = 0.f;
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) {
+            const int p = jp * 256 + t;
+            float2 v;
+            if (Vin) v = Vin[(size_t)k * N_SC + p];
+            else {
+                const float2 h = H[(size_t)k * N_SC + p];
+                v = make_float2(h.x * ninv[jp], -h.y * ninv[jp]);
+            }
+            pw = fmaf(v.x, v.x, fmaf(v.y, v.y, pw));
+            Vout[(size_t)k * N_SC + p] = make_float2(v.x * 0.015625f, v.y * 0.015625f);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) pw += __shfl_xor_sync(0xffffffffu, pw, o);
+        if ((t & 31) == 0) part_s[k][t >> 5] = pw;
+    }
+    __syncthreads();
+    if (t < K) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += (double)part_s[t][w];
+        vkpow_s[t] = s;
+        // mp_model.py:315-317 + modulation.py:178-189
+        const double g2 = a.ibo_lin * (double)N_SC / (s * (double)K);
+        const double g = sqrt(g2);
+        const double al = 1.0 - exp(-g2) + (1.7724538509055160273 * g * 0.5) * erfc(g);
+        alpha_s[t] = (float)al;
+        if (a.alpha_out) a.alpha_out[(size_t)f * K + t] = (float)al;
+    }
+    __syncthreads();
+    // AGC vectors
+    float2 agc[8], hv[8];
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) agc[jp] = hv[jp] = make_float2(0.f, 0.f);
+    for (int k = 0; k < K; ++k) {
+        const float al = alpha_s[k];
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) {
+            const int p = jp * 256 + t;
+            const float2 h = H[(size_t)k * N_SC + p];
+            float2 v;
+            if (Vin) v = Vin[(size_t)k * N_SC + p];
+            else v = make_float2(h.x * ninv[jp], -h.y * ninv[jp]);
+            const float2 m = cmul(h, v);
+            hv[jp] = cadd(hv[jp], m);
+            agc[jp] = make_float2(fmaf(al, m.x, agc[jp].x), fmaf(al, m.y, agc[jp].y));
+        }
+    }
+    double s_agc = 0.0, s_hv = 0.0;
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        const int p = jp * 256 + t;
+        const double a2 = (double)agc[jp].x * agc[jp].x + (double)agc[jp].y * agc[jp].y;
+        const double h2 = (double)hv[jp].x * hv[jp].x + (double)hv[jp].y * hv[jp].y;
+        s_agc += a2; s_hv += h2;
+        // 1/z = conj(z)/|z|^2
+        a.agc_inv[(size_t)f * N_SC + p] = make_float2((float)(agc[jp].x / (64.0 * a2)), (float)(-agc[jp].y / (64.0 * a2)));
+        a.hkvk_inv[(size_t)f * N_SC + p] = make_float2((float)(hv[jp].x / h2), (float)(-hv[jp].y / h2));
+    }
+    s_agc = block_sum_256(s_agc, red_s, t);
+    s_hv = block_sum_256(s_hv, red_s, t);
+    if (t == 0) {
+        double tot = 0.0;
+        for (int k = 0; k < K; ++k) tot += vkpow_s[k];
+        const double gain = tot / ((double)K * N_SC);           // antenna_array.py:328-341
+        const double avg = a.avg_sample_power * gain;
+        FrameScalars sc;
+        const double p0_tx = (a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / avg : a.ibo_lin * avg;  // distortion.py:37,228
+        // CNC loop PA: avg_samp_pow = avg_symbol_power * n_sub_carr / n_fft (corrector.py:34-35)
+        const double p0_cnc = (a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / a.avg_sample_power : a.ibo_lin * a.avg_sample_power;
+        sc.pa_p0_tx = (float)p0_tx;
+        sc.pa_p0_loop = (float)(a.is_mcnc ? p0_tx : p0_cnc);
+        // noise.py:64-66: component std = 0.5*sqrt(2 P / snr), P = avg_symbol_power * noise_scaler
+        sc.noise_sigma = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_agc / N_SC) / a.snr_lin));
+        sc.noise_sigma_clean = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_hv / N_SC) / a.snr_lin));
+        a.scal[f] = sc;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_clean_frame: the "no distortion" loop body (mp_model.py:158-173).  FFT(IFFT(x)) == x, so it is
+// precode -> channel -> noise -> / sum_k h_k v_k -> slice -> count.  One CTA per frame.
+// ---------------------------------------------------------------------------------------------
+struct CleanArgs {
+    const float2* h_true; long long h_fs;
+    const float2* v;      long long v_fs;   // pre-scaled by 1/64 (as written by k_prep_realisation)
+    const float2* hkvk_inv;                 // [F][2048]
+    const FrameScalars* scal;
+    int n_ant, n_frames;
+    Qam qam;
+    const uint8_t* tx_idx; const float2* noise;
+    uint64_t seed, frame_id0;
+    uint8_t* det_out;            // [F][2048] or nullptr
+    uint32_t* err_out;           // [F] or nullptr
+    unsigned long long* err_total;  // [1]
+};
+
+__global__ void __launch_bounds__(256) k_clean_frame(const CleanArgs a) {
+    __shared__ unsigned int err_s;
+    const int f = blockIdx.x, t = threadIdx.x;
+    if (t == 0) err_s = 0;
+    __syncthreads();
+    const FrameScalars sc = a.scal[f];
+    uint32_t txw[2] = {0u, 0u};
+    if (a.tx_idx) {
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)a.tx_idx[(size_t)f * N_SC + jp * 256 + t] << (8 * (jp & 3));
+    } else {
+        uint32_t r[4];
+        const uint64_t fid = a.frame_id0 + f;
+        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_CLEAN_BITS, (uint32_t)t, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+        const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+        const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+        txw[0] = r[0] & m4; txw[1] = r[1] & m4;
+    }
+    float2 g[8];
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) g[jp] = make_float2(0.f, 0.f);
+    const float2* __restrict__ H = a.h_true + f * a.h_fs;
+    const float2* __restrict__ V = a.v + f * a.v_fs;
+    for (int k = 0; k < a.n_ant; ++k) {
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) g[jp] = cfma(H[(size_t)k * N_SC + jp * 256 + t], V[(size_t)k * N_SC + jp * 256 + t], g[jp]);
+    }
+    float2 nz[8];
+    if (a.noise) {
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) nz[jp] = a.noise[(size_t)f * N_SC + jp * 256 + t];
+    } else {
+        const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r[4];
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_CLEAN_NOISE, (uint32_t)(t * 4 + q), (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+            const float2 g0 = box_muller(r[0], r[1]), g1 = box_muller(r[2], r[3]);
+            nz[2 * q] = make_float2(g0.x * sc.noise_sigma_clean, g0.y * sc.noise_sigma_clean);
+            nz[2 * q + 1] = make_float2(g1.x * sc.noise_sigma_clean, g1.y * sc.noise_sigma_clean);
+        }
+    }
+    uint32_t detw[2] = {0u, 0u};
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        const int p = jp * 256 + t;
+        const float2 s = qam_symbol(a.qam, (txw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+        // g holds sum h v / 64
+        const float2 y = cadd(cmul(make_float2(64.f * g[jp].x, 64.f * g[jp].y), s), nz[jp]);
+        const uint32_t idx = qam_detect(a.qam, cmul(y, a.hkvk_inv[(size_t)f * N_SC + p]));
+        detw[jp >> 2] |= idx << (8 * (jp & 3));
+        if (a.det_out) a.det_out[(size_t)f * N_SC + p] = (uint8_t)idx;
+    }
+    unsigned int nerr = __popc(detw[0] ^ txw[0]) + __popc(detw[1] ^ txw[1]);
+    nerr = __reduce_add_sync(0xffffffffu, nerr);
+    if ((t & 31) == 0) atomicAdd(&err_s, nerr);
+    __syncthreads();
+    if (t == 0) {
+        if (a.err_out) a.err_out[f] = err_s;
+        atomicAdd(a.err_total, (unsigned long long)err_s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_gen_rayleigh: MisoRayleighFd (channel.py:187-292): IID CN(0,1) coefficients times the free-space
+// loss evaluated at the NOMINAL receiver position (the attenuation is fixed at construction).
+// ---------------------------------------------------------------------------------------------
+struct RayleighArgs {
+    const double* tx_pos; const double* freq_slot;
+    double rx0[3]; double gain_lin; int skip_attenuation;
+    uint64_t seed, frame_id0; uint32_t stream;
+    float2* h_out; int n_ant;
+};
+
+__global__ void __launch_bounds__(256) k_gen_rayleigh(const RayleighArgs a) {
+    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
+    const double dx = a.tx_pos[k * 3 + 0] - a.rx0[0], dy = a.tx_pos[k * 3 + 1] - a.rx0[1], dz = a.tx_pos[k * 3 + 2] - a.rx0[2];
+    const double d = sqrt(dx * dx + dy * dy + dz * dz);
+    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+    const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint32_t r[4];
+        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
+                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+        const float2 g[2] = {box_muller(r[0], r[1]), box_muller(r[2], r[3])};
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int p = (2 * q + e) * 256 + t;
+            float att = 0.70710678118654752440f;
+            if (!a.skip_attenuation) att *= (float)(a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846 * d * a.freq_slot[p]));
+            out[p] = make_float2(g[e].x * att, g[e].y * att);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_csi_error: mp_model.py:264-284, h_hat = sqrt(1-eps^2) h + eps CN(0, mean_s |h_k[s]|^2) per antenna.
+// ---------------------------------------------------------------------------------------------
+struct CsiArgs {
+    const float2* h_in; float2* h_out; float eps, scale;
+    uint64_t seed, frame_id0; uint32_t stream; int n_ant;
+};
+
+__global__ void __launch_bounds__(256) k_csi_error(const CsiArgs a) {
+    __shared__ double red_s[8];
+    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
+    const float2* in = a.h_in + ((size_t)f * a.n_ant + k) * N_SC;
+    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+    float2 h[8];
+    double pw = 0.0;
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        h[jp] = in[jp * 256 + t];
+        pw += (double)h[jp].x * h[jp].x + (double)h[jp].y * h[jp].y;
+    }
+    pw = block_sum_256(pw, red_s, t) / N_SC;
+    const float sig = a.eps * (float)sqrt(0.5 * pw);
+    const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint32_t r[4];
+        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
+                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+        const float2 g[2] = {box_muller(r[0], r[1]), box_muller(r[2], r[3])};
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int jp = 2 * q + e;
+            out[jp * 256 + t] = make_float2(fmaf(a.scale, h[jp].x, sig * g[e].x), fmaf(a.scale, h[jp].y, sig * g[e].y));
+        }
+    }
+}
+
+}  // namespace mmimo

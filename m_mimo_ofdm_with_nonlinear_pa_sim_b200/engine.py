@@ -1,0 +1,194 @@
+"""Host-side handle on one GPU context of libmmimo_b200.so: the fused Monte-Carlo link
+(`Link.simulate`, mp_model.py:89-222) for batches of frames.  numpy in / numpy out; all compute is CUDA."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+
+C_LIGHT = 299792458.0  # scipy.constants.c
+
+PA_KINDS = {"none": 0, "softlim": 1, "rapp": 2, "toi": 3}
+CHAN_KINDS = {"los": 0, "two_path": 1, "rayleigh": 2, "injected": 3}
+RX_KINDS = {"cnc": 0, "mcnc": 1}
+N_FFT, N_SC = 4096, 2048
+
+
+def ula_positions(n_elements: int, center_freq: float, wav_len_spacing: float, cord_x=0.0, cord_y=0.0, cord_z=15.0):
+    """Element coordinates of LinearArray (antenna_array.py:436-445): ULA along X centred on cord_x."""
+    lam = C_LIGHT / center_freq
+    half = (n_elements - 1) * wav_len_spacing * lam / 2
+    x = np.linspace(-half, half, n_elements) + cord_x
+    return np.stack((x, np.full(n_elements, float(cord_y)), np.full(n_elements, float(cord_z))), axis=1)
+
+
+def subcarrier_freqs(n_fft: int, carrier_spacing: float, center_freq: float) -> np.ndarray:
+    """Sub-carrier frequencies exactly as channel.py:51-52 produces them: torch.fft.fftfreq is float32 and
+    stays float32 through `* spacing + fc`, i.e. the values sit on the float32 grid (256 Hz at 3.5 GHz)."""
+    k = np.fft.fftfreq(n_fft, d=1.0 / n_fft).astype(np.float32)
+    f32 = k * np.float32(carrier_spacing) + np.float32(center_freq)
+    return f32.astype(np.float64)
+
+
+def _ptr(arr, ctype):
+    return arr.ctypes.data_as(C.POINTER(ctype)) if arr is not None else None
+
+
+def _c64(a, shape):
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.complex64))
+    if a.shape != tuple(shape):
+        raise ValueError("expected shape %s, got %s" % (tuple(shape), a.shape))
+    return a
+
+
+class LinkEngine:
+    """One mmimo_ctx (one GPU).  Not thread-safe; create it in the process that uses it (CUDA contexts do
+    not survive fork)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        _lib.check(self._lib, self._lib.mmimo_create(C.byref(h), int(device)))
+        self._h = h
+        self.device = int(device)
+        self.cfg = None
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.mmimo_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------------------------------
+    def configure(self, *, constel_size=64, n_fft=N_FFT, n_sub_carr=N_SC, n_ant=64, pa="softlim", ibo_db=0.0,
+                  p_hardness=4.0, channel="los", receiver="mcnc", skip_attenuation=False, center_freq=3.5e9,
+                  carrier_spacing=15e3, wav_len_spacing=0.5, array_pos=(0.0, 0.0, 15.0), rx_pos=(212.0, 212.0, 1.5),
+                  rx_loc_var=10.0, ant_gain_db=0.0, tx_pos=None, freqs=None):
+        if tx_pos is None:
+            tx_pos = ula_positions(n_ant, center_freq, wav_len_spacing, *array_pos)
+        tx_pos = np.ascontiguousarray(np.asarray(tx_pos, dtype=np.float64).reshape(n_ant, 3))
+        if freqs is None:
+            freqs = subcarrier_freqs(n_fft, carrier_spacing, center_freq)
+        freqs = np.ascontiguousarray(np.asarray(freqs, dtype=np.float64).reshape(n_fft))
+        cfg = _lib.LinkConfig()
+        cfg.constel_size, cfg.n_fft, cfg.n_sub_carr, cfg.n_ant = int(constel_size), int(n_fft), int(n_sub_carr), int(n_ant)
+        cfg.pa_kind = PA_KINDS[pa] if isinstance(pa, str) else int(pa)
+        cfg.channel_kind = CHAN_KINDS[channel] if isinstance(channel, str) else int(channel)
+        cfg.receiver_kind = RX_KINDS[receiver] if isinstance(receiver, str) else int(receiver)
+        cfg.skip_attenuation = int(bool(skip_attenuation))
+        cfg.ibo_db, cfg.p_hardness = float(ibo_db), float(p_hardness)
+        cfg.center_freq, cfg.carrier_spacing = float(center_freq), float(carrier_spacing)
+        cfg.rx_pos = (C.c_double * 3)(*[float(v) for v in rx_pos])
+        cfg.rx_loc_var, cfg.ant_gain_db = float(rx_loc_var), float(ant_gain_db)
+        cfg.tx_pos = _ptr(tx_pos, C.c_double)
+        cfg.freqs = _ptr(freqs, C.c_double)
+        _lib.check(self._lib, self._lib.mmimo_configure(self._h, C.byref(cfg)))
+        self.cfg = dict(constel_size=int(constel_size), n_fft=int(n_fft), n_sub_carr=int(n_sub_carr), n_ant=int(n_ant),
+                        pa=pa, ibo_db=float(ibo_db), channel=channel, receiver=receiver, tx_pos=tx_pos, freqs=freqs)
+        self.bits_per_frame = int(math.log2(constel_size)) * n_sub_carr
+        return self
+
+    def set_ibo(self, ibo_db: float):
+        _lib.check(self._lib, self._lib.mmimo_set_ibo(self._h, float(ibo_db)))
+        self.cfg["ibo_db"] = float(ibo_db)
+
+    # ------------------------------------------------------------------------------------------
+    def _request(self, n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject):
+        K = self.cfg["n_ant"]
+        rq = _lib.SimRequest()
+        rq.n_frames, rq.n_iter, rq.incl_clean_run = int(n_frames), int(n_iter), int(bool(incl_clean_run))
+        rq.snr_db, rq.csi_eps = float(snr_db), float(csi_eps or 0.0)
+        rq.seed, rq.frame_id0 = int(seed) & (2 ** 64 - 1), int(frame_id0)
+        keep = []
+        inject = inject or {}
+        unknown = set(inject) - {"rx_pos", "h_true", "h_loop", "tx_idx", "noise", "clean_rx_pos", "clean_h_true",
+                                 "clean_h_loop", "clean_tx_idx", "clean_noise"}
+        if unknown:
+            raise ValueError("unknown injected inputs: %s" % sorted(unknown))
+        for pre in ("", "clean_"):
+            v = inject.get(pre + "rx_pos")
+            if v is not None:
+                a = np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(n_frames, 3))
+                keep.append(a)
+                setattr(rq, pre + "rx_pos", _ptr(a, C.c_double))
+            for name in ("h_true", "h_loop"):
+                v = inject.get(pre + name)
+                if v is not None:
+                    a = _c64(v, (n_frames, K, N_SC))
+                    keep.append(a)
+                    setattr(rq, pre + name, _ptr(a, C.c_float))
+            v = inject.get(pre + "tx_idx")
+            if v is not None:
+                a = np.ascontiguousarray(np.asarray(v, dtype=np.uint8).reshape(n_frames, N_SC))
+                keep.append(a)
+                setattr(rq, pre + "tx_idx", _ptr(a, C.c_uint8))
+            v = inject.get(pre + "noise")
+            if v is not None:
+                a = _c64(v, (n_frames, N_SC))
+                keep.append(a)
+                setattr(rq, pre + "noise", _ptr(a, C.c_float))
+        return rq, keep
+
+    def simulate(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
+                 inject=None, dumps=()):
+        """Run `n_frames` frames; returns dict(err=[n_iter+1], bits=..., clean_err, + requested dumps).
+
+        dumps: any of det, err_per_frame, rx_eq, corr, h_true, v, agc, pa_p0, alpha, rx_pos, clean_det."""
+        if self.cfg is None:
+            raise _lib.MmimoError("LinkEngine.configure() has not been called")
+        K, I = self.cfg["n_ant"], int(n_iter)
+        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject)
+        rs = _lib.SimResult()
+        out = {"err": np.zeros(I + 1, dtype=np.uint64), "clean_err": np.zeros(1, dtype=np.uint64)}
+        rs.err, rs.clean_err = _ptr(out["err"], C.c_uint64), _ptr(out["clean_err"], C.c_uint64)
+        shapes = {"det": ((n_frames, I + 1, N_SC), np.uint8, C.c_uint8),
+                  "err_per_frame": ((n_frames, I + 1), np.uint32, C.c_uint32),
+                  "rx_eq": ((n_frames, N_SC), np.complex64, C.c_float),
+                  "corr": ((n_frames, I + 1, N_SC), np.complex64, C.c_float),
+                  "h_true": ((n_frames, K, N_SC), np.complex64, C.c_float),
+                  "v": ((n_frames, K, N_SC), np.complex64, C.c_float),
+                  "agc": ((n_frames, N_SC), np.complex64, C.c_float),
+                  "pa_p0": ((n_frames,), np.float32, C.c_float),
+                  "alpha": ((n_frames, K), np.float32, C.c_float),
+                  "rx_pos": ((n_frames, 3), np.float64, C.c_double),
+                  "clean_det": ((n_frames, N_SC), np.uint8, C.c_uint8)}
+        for name in dumps:
+            shape, dt, ct = shapes[name]
+            out[name] = np.zeros(shape, dtype=dt)
+            setattr(rs, name, _ptr(out[name], ct))
+        _lib.check(self._lib, self._lib.mmimo_link_simulate(self._h, C.byref(rq), C.byref(rs)))
+        del keep
+        out["bits_per_frame"] = int(rs.bits_per_frame)
+        out["bits"] = int(rs.bits_per_frame) * int(n_frames)
+        return out
+
+    def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0):
+        """Asynchronous: kernels only, counters accumulate on the device until fetch()."""
+        rq, _ = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, None)
+        _lib.check(self._lib, self._lib.mmimo_link_enqueue(self._h, C.byref(rq)))
+
+    def fetch(self, n_iter):
+        err = np.zeros(int(n_iter) + 1, dtype=np.uint64)
+        clean = np.zeros(1, dtype=np.uint64)
+        _lib.check(self._lib, self._lib.mmimo_link_fetch(self._h, int(n_iter), _ptr(err, C.c_uint64), _ptr(clean, C.c_uint64)))
+        return err, clean
+
+    def synchronize(self):
+        _lib.check(self._lib, self._lib.mmimo_synchronize(self._h))
+
+    @property
+    def stream_ptr(self) -> int:
+        return int(self._lib.mmimo_stream(self._h) or 0)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.mmimo_launch_count(self._h))
