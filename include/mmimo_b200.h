@@ -106,6 +106,9 @@ const char* mmimo_last_error(void);
 const char* mmimo_version(void);
 void* mmimo_stream(mmimo_ctx* ctx);            /* cudaStream_t all work of this context is enqueued on */
 int mmimo_synchronize(mmimo_ctx* ctx);
+/* run all further work of this context on the caller's cudaStream_t (NULL = back to the context's own stream);
+ * lets the host side order kernels against torch.distributed collectives without extra synchronisation */
+int mmimo_set_stream(mmimo_ctx* ctx, void* cuda_stream);
 
 /* Link.__init__ / update_distortion (mp_model.py:32-87, :230-241): (re)describe the link */
 int mmimo_configure(mmimo_ctx* ctx, const mmimo_link_config* cfg);
@@ -118,8 +121,20 @@ int mmimo_set_ibo(mmimo_ctx* ctx, double ibo_db);
 int mmimo_link_simulate(mmimo_ctx* ctx, const mmimo_sim_request* req, mmimo_sim_result* res);
 int mmimo_link_enqueue(mmimo_ctx* ctx, const mmimo_sim_request* req);
 int mmimo_link_fetch(mmimo_ctx* ctx, int32_t n_iter, uint64_t* err, uint64_t* clean_err);
+/* stream-ordered copy of the 65 uint64 device counters ([0..63] bit errors after iteration i, [64] clean run)
+ * into caller-owned DEVICE memory - the buffer handed to the NCCL all-reduce that replaces the shared
+ * multiprocessing.Array accumulation of mp_model.py:172-173,221-222; clear != 0 zeroes the counters after the copy */
+int mmimo_counters_to_device(mmimo_ctx* ctx, void* dst_dev, int clear);
 /* number of kernels launched by this context so far (bench.py "gpu_launches") */
 uint64_t mmimo_launch_count(mmimo_ctx* ctx);
+
+
+/* measurement helpers (bench.py): per-kernel CUDA-event timing on the context's stream.
+ * kinds: 0 channel generation, 1 realisation prep (precoder/AGC), 2 fused frame kernel, 3 other */
+int mmimo_profile(mmimo_ctx* ctx, int enable);
+int mmimo_profile_read(mmimo_ctx* ctx, double* ms4, uint64_t* n4);
+/* measured FP32 FMA peak of the device in TFLOP/s (dependent-free FFMA chains on every SM) */
+int mmimo_measure_fp32_peak(mmimo_ctx* ctx, double* tflops);
 
 #ifdef __cplusplus
 }

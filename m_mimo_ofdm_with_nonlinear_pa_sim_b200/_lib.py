@@ -41,8 +41,9 @@ _LIB = None
 
 # every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = ["mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
+           "mmimo_set_stream", "mmimo_counters_to_device",
            "mmimo_configure", "mmimo_set_ibo", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
-           "mmimo_launch_count"]
+           "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak"]
 
 
 def lib_path() -> str:
@@ -73,6 +74,8 @@ def load(build_if_missing: bool = True):
     lib.mmimo_stream.argtypes = [C.c_void_p]
     lib.mmimo_stream.restype = C.c_void_p
     lib.mmimo_synchronize.argtypes = [C.c_void_p]
+    lib.mmimo_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+    lib.mmimo_counters_to_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     lib.mmimo_configure.argtypes = [C.c_void_p, C.POINTER(LinkConfig)]
     lib.mmimo_set_ibo.argtypes = [C.c_void_p, C.c_double]
     lib.mmimo_link_simulate.argtypes = [C.c_void_p, C.POINTER(SimRequest), C.POINTER(SimResult)]
@@ -80,6 +83,9 @@ def load(build_if_missing: bool = True):
     lib.mmimo_link_fetch.argtypes = [C.c_void_p, C.c_int32, c_u64_p, c_u64_p]
     lib.mmimo_launch_count.argtypes = [C.c_void_p]
     lib.mmimo_launch_count.restype = C.c_uint64
+    lib.mmimo_profile.argtypes = [C.c_void_p, C.c_int]
+    lib.mmimo_profile_read.argtypes = [C.c_void_p, c_d_p, c_u64_p]
+    lib.mmimo_measure_fp32_peak.argtypes = [C.c_void_p, c_d_p]
     _bind_stage_ops(lib)
     _LIB = lib
     return lib

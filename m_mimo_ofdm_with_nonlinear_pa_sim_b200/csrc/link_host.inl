@@ -66,7 +66,9 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ca.seed = rq->seed; ca.frame_id0 = rq->frame_id0 + c0;
         ca.pos_stream = in.pos_stream;
         ca.h_out = h_true; ca.n_ant = K;
+        prof_begin(c, PROF_CHAN);
         k_gen_channel<<<dim3(K, n), 256, 0, c->stream>>>(ca);
+        prof_end(c);
         c->launches++;
     } else if (cfg.channel_kind == MMIMO_CHAN_RAYLEIGH) {
         RayleighArgs ra{};
@@ -77,7 +79,9 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ra.skip_attenuation = cfg.skip_attenuation;
         ra.seed = rq->seed; ra.frame_id0 = rq->frame_id0 + c0; ra.stream = in.ray_stream;
         ra.h_out = h_true; ra.n_ant = K;
+        prof_begin(c, PROF_CHAN);
         k_gen_rayleigh<<<dim3(K, n), 256, 0, c->stream>>>(ra);
+        prof_end(c);
         c->launches++;
     } else {
         return fail("mmimo_link: channel_kind INJECTED needs h_true in the request");
@@ -109,7 +113,9 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     pa.avg_symbol_power = avg_symbol_power(cfg.constel_size);
     pa.avg_sample_power = pa.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
     pa.snr_lin = pow(10.0, rq->snr_db / 10.0);
+    prof_begin(c, PROF_PREP);
     k_prep_realisation<<<n, 256, 0, c->stream>>>(pa);
+    prof_end(c);
     c->launches++;
     *h_true_out = h_true;
     *h_loop_out = h_loop;
@@ -224,12 +230,14 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
         fa.err_total = counters;
         const int grid = std::min(n, 2 * c->n_sm);
+        prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {
             case MMIMO_PA_NONE: launch_frame<PA_NONE>(fa, c, grid); break;
             case MMIMO_PA_SOFT_LIMITER: launch_frame<PA_SOFT_LIMITER>(fa, c, grid); break;
             case MMIMO_PA_RAPP: launch_frame<PA_RAPP>(fa, c, grid); break;
             default: launch_frame<PA_TOI>(fa, c, grid); break;
         }
+        prof_end(c);
         c->launches++;
         CK(cudaGetLastError());
 

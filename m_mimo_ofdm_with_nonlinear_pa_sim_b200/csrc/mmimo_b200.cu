@@ -54,6 +54,7 @@ struct DevBuf {
 struct mmimo_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;
     bool configured = false;
     mmimo_link_config cfg{};
     std::vector<double> tx_pos_h, freqs_h;
@@ -68,7 +69,26 @@ struct mmimo_ctx {
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // stage-op scratch
     DevBuf s_a, s_b, s_c, s_d;
+    // optional per-kernel CUDA-event timing (mmimo_profile)
+    struct ProfRec { int kind; cudaEvent_t a, b; };
+    bool prof = false;
+    std::vector<ProfRec> prof_recs;
 };
+
+enum { PROF_CHAN = 0, PROF_PREP = 1, PROF_FRAME = 2, PROF_OTHER = 3 };
+static void prof_begin(mmimo_ctx* c, int kind) {
+    if (!c->prof) return;
+    mmimo_ctx::ProfRec r;
+    r.kind = kind;
+    cudaEventCreate(&r.a);
+    cudaEventCreate(&r.b);
+    cudaEventRecord(r.a, c->stream);
+    c->prof_recs.push_back(r);
+}
+static void prof_end(mmimo_ctx* c) {
+    if (!c->prof || c->prof_recs.empty()) return;
+    cudaEventRecord(c->prof_recs.back().b, c->stream);
+}
 
 template <class T>
 __global__ void k_to_native(const T* __restrict__ src, T* __restrict__ dst, size_t rows) {
@@ -121,7 +141,8 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     mmimo_ctx* c = new mmimo_ctx();
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
-    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
     // twiddle tables, computed in double (forward sign)
     std::vector<float2> t4(4096), t2(256);
     for (int i = 0; i < 4096; ++i) {
@@ -155,11 +176,25 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
                      &c->s_a, &c->s_b, &c->s_c, &c->s_d};
     for (DevBuf* b : all) b->release();
-    cudaStreamDestroy(c->stream);
+    cudaStreamDestroy(c->own_stream);
     delete c;
 }
 
 extern "C" void* mmimo_stream(mmimo_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int mmimo_set_stream(mmimo_ctx* c, void* stream) {
+    if (!c) return fail("NULL context");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+    return 0;
+}
+extern "C" int mmimo_counters_to_device(mmimo_ctx* c, void* dst_dev, int clear) {
+    if (!c || !dst_dev) return fail("NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst_dev, c->counters.p, 65 * 8, cudaMemcpyDeviceToDevice, c->stream));
+    if (clear) CK(cudaMemsetAsync(c->counters.p, 0, 65 * 8, c->stream));
+    return 0;
+}
 extern "C" uint64_t mmimo_launch_count(mmimo_ctx* c) { return c ? c->launches : 0; }
 extern "C" int mmimo_synchronize(mmimo_ctx* c) {
     if (!c) return fail("NULL context");
@@ -211,6 +246,72 @@ extern "C" int mmimo_configure(mmimo_ctx* c, const mmimo_link_config* cfg) {
 extern "C" int mmimo_set_ibo(mmimo_ctx* c, double ibo_db) {
     if (!c || !c->configured) return fail("mmimo_set_ibo: context not configured");
     c->cfg.ibo_db = ibo_db;
+    return 0;
+}
+
+extern "C" int mmimo_profile(mmimo_ctx* c, int enable) {
+    if (!c) return fail("NULL context");
+    c->prof = enable != 0;
+    return 0;
+}
+
+extern "C" int mmimo_profile_read(mmimo_ctx* c, double* ms4, uint64_t* n4) {
+    if (!c) return fail("NULL context");
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 4; ++i) { if (ms4) ms4[i] = 0.0; if (n4) n4[i] = 0; }
+    for (auto& r : c->prof_recs) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        if (ms4) ms4[r.kind] += ms;
+        if (n4) n4[r.kind] += 1;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    c->prof_recs.clear();
+    return 0;
+}
+
+// FP32 FMA peak of this device, measured: 16 independent FFMA chains per thread
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
+    float x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = (float)(threadIdx.x + i);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i] = fmaf(x[i], a, b);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += x[i];
+    if (s == 123.456f) out[0] = s;
+}
+
+extern "C" int mmimo_measure_fp32_peak(mmimo_ctx* c, double* tflops) {
+    if (!c || !tflops) return fail("NULL argument");
+    CK(cudaSetDevice(c->device));
+    if (c->s_d.reserve(64)) return 1;
+    const int iters = 4096, grid = c->n_sm * 8;
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        CK(cudaEventRecord(a, c->stream));
+        k_fma_peak<<<grid, 256, 0, c->stream>>>(c->s_d.as<float>(), iters, 0.999f, 0.001f);
+        CK(cudaEventRecord(b, c->stream));
+        CK(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        const double fl = 2.0 * 16 * 8 * (double)iters * 256.0 * grid;
+        if (rep > 0) best = std::max(best, fl / (ms * 1e-3) * 1e-12);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    c->launches += 6;
+    *tflops = best;
     return 0;
 }
 

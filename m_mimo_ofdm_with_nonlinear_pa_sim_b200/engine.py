@@ -171,19 +171,47 @@ class LinkEngine:
         out["bits"] = int(rs.bits_per_frame) * int(n_frames)
         return out
 
-    def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0):
-        """Asynchronous: kernels only, counters accumulate on the device until fetch()."""
-        rq, _ = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, None)
+    def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
+                inject=None):
+        """Asynchronous: H2D of injected inputs + kernels, counters accumulate on the device until fetch().
+        Injected host arrays are kept alive until the next fetch()/synchronize()."""
+        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject)
+        self._keep.append(keep)
         _lib.check(self._lib, self._lib.mmimo_link_enqueue(self._h, C.byref(rq)))
 
     def fetch(self, n_iter):
         err = np.zeros(int(n_iter) + 1, dtype=np.uint64)
         clean = np.zeros(1, dtype=np.uint64)
         _lib.check(self._lib, self._lib.mmimo_link_fetch(self._h, int(n_iter), _ptr(err, C.c_uint64), _ptr(clean, C.c_uint64)))
+        self._keep.clear()
         return err, clean
+
+    def set_stream(self, cuda_stream_ptr: int = 0):
+        """Enqueue all further work on the given cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream)."""
+        _lib.check(self._lib, self._lib.mmimo_set_stream(self._h, C.c_void_p(int(cuda_stream_ptr) or None)))
+
+    def counters_to_device(self, dst_dev_ptr: int, clear: bool = True):
+        """Stream-ordered D2D copy of the 65 uint64 error counters into caller-owned device memory."""
+        _lib.check(self._lib, self._lib.mmimo_counters_to_device(self._h, C.c_void_p(int(dst_dev_ptr)), int(bool(clear))))
 
     def synchronize(self):
         _lib.check(self._lib, self._lib.mmimo_synchronize(self._h))
+        self._keep.clear()
+
+    def profile(self, enable: bool):
+        _lib.check(self._lib, self._lib.mmimo_profile(self._h, int(bool(enable))))
+
+    def profile_read(self):
+        """(ms per kind, launches per kind) for kinds (channel, prep, frame, other); clears the records."""
+        ms = np.zeros(4, dtype=np.float64)
+        n = np.zeros(4, dtype=np.uint64)
+        _lib.check(self._lib, self._lib.mmimo_profile_read(self._h, _ptr(ms, C.c_double), _ptr(n, C.c_uint64)))
+        return ms, n
+
+    def measure_fp32_peak(self) -> float:
+        v = C.c_double()
+        _lib.check(self._lib, self._lib.mmimo_measure_fp32_peak(self._h, C.byref(v)))
+        return float(v.value)
 
     @property
     def stream_ptr(self) -> int:

@@ -1,0 +1,163 @@
+"""GPU parity of the fused link kernels (through the C ABI) against the reference's own outputs
+(tests/golden/*.npz) and the CPU oracle, with the reference's bits / receiver positions / channel /
+noise injected.  Tolerances: complex stages 1e-5 relative L2 (fp32 compute vs complex128, BASELINE.json
+north_star); hard decisions and error counts bit-exact, where a frame is only compared up to the first
+iteration in which the ORACLE's slicer input sits closer than MARGIN to a decision boundary (an fp32
+result may legitimately fall on the other side there, and MCNC feeds the decision back)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, rel_l2
+from oracle import link_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5      # relative L2, complex stages
+MARGIN = 2e-4   # absolute distance to a slicer boundary below which an fp32 flip is tolerated
+
+GOLDEN_4096 = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k8_los_csi",
+               "link_k8_los_rapp"]
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    eng = LinkEngine(0)
+    yield eng
+    eng.close()
+
+
+def cfg_from_golden(g):
+    pa = {"softlim": lo.PA_SOFT_LIMITER, "rapp": lo.PA_RAPP, "toi": lo.PA_TOI}[str(g["pa"])]
+    return lo.LinkConfig(constel_size=int(g["constel"]), n_fft=int(g["n_fft"]), n_sub_carr=int(g["n_sc"]),
+                         n_ant=int(g["n_ant"]), pa_kind=pa, ibo_db=float(g["ibo_db"]), channel=str(g["chan"]))
+
+
+def oracle_run(cfg, snr_db, n_iter, seeds, n_frames, is_mcnc, incl_clean, csi):
+    """Oracle frames incl. everything that gets injected into the GPU path."""
+    # the clean loop consumes the RNG streams first (mp_model.py:136-175); the oracle handles that
+    return lo.link_simulate(cfg, snr_db, n_iter, seeds, n_frames, is_mcnc=is_mcnc, incl_clean_run=incl_clean,
+                            csi_eps=csi, return_frames=True)
+
+
+def compare_decisions(det_gpu, det_ref, corr_ref, constel, iters=None):
+    """det_*: [I+1, N_sc].  Returns (n_iterations_compared_exactly, diverged?)."""
+    n_it = det_ref.shape[0]
+    for it in range(n_it):
+        mism = det_gpu[it] != det_ref[it]
+        if mism.any():
+            m = lo.detection_margin(corr_ref[it][mism], constel)
+            assert m.max() < MARGIN, "iteration %d: %d decisions differ with margin up to %.3g" % (it, mism.sum(), m.max())
+            return it, True
+    return n_it, False
+
+
+def run_case(engine, cfg, snr_db, iters, seeds, n_frames, is_mcnc, incl_clean, csi, golden=None):
+    n_iter = int(np.max(iters))
+    errs, bits, frames = oracle_run(cfg, snr_db, n_iter, seeds, n_frames, is_mcnc, incl_clean, csi)
+    pa = {lo.PA_SOFT_LIMITER: "softlim", lo.PA_RAPP: "rapp", lo.PA_TOI: "toi"}[cfg.pa_kind]
+    engine.configure(constel_size=cfg.constel_size, n_ant=cfg.n_ant, pa=pa, ibo_db=cfg.ibo_db,
+                     p_hardness=cfg.p_hardness, channel="injected", receiver="mcnc" if is_mcnc else "cnc")
+    bins = cfg.bins
+    inject = dict(h_true=np.stack([f["real"].h_true[:, bins] for f in frames]),
+                  tx_idx=np.stack([f["tx_idx"] for f in frames]),
+                  noise=np.stack([f["noise"][bins] for f in frames]))
+    if csi is not None:
+        inject["h_loop"] = np.stack([f["real"].h_loop[:, bins] for f in frames])
+    out = engine.simulate(n_frames, n_iter, snr_db, inject=inject,
+                          dumps=("det", "err_per_frame", "rx_eq", "corr", "v", "agc", "pa_p0", "alpha"))
+    n_div = 0
+    for i, fr in enumerate(frames):
+        real = fr["real"]
+        assert rel_l2(out["v"][i], real.v) < TOL
+        assert rel_l2(out["agc"][i], real.ak_hk_vk_agc) < TOL
+        assert abs(out["pa_p0"][i] / real.pa[1] - 1) < TOL
+        assert np.allclose(out["alpha"][i], real.alpha_k, rtol=1e-5)
+        assert rel_l2(out["rx_eq"][i], fr["rx_eq_sc"]) < TOL
+        corr_ref = fr["corr"]
+        n_ok, div = compare_decisions(out["det"][i].astype(np.int64), fr["det"], corr_ref, cfg.constel_size)
+        n_div += div
+        for it in range(n_ok):
+            assert rel_l2(out["corr"][i, it], corr_ref[it]) < 5 * TOL
+            assert out["err_per_frame"][i, it] == fr["err"][it]
+        if golden is not None:  # the reference's own outputs
+            gdet = golden["det"][i].astype(np.int64)
+            sel = [k for k, itv in enumerate(iters) if itv < n_ok]
+            assert np.array_equal(out["det"][i][np.asarray(iters)[sel]], gdet[sel])
+            assert rel_l2(out["rx_eq"][i], golden["rx_eq_sc"][i]) < TOL
+            assert rel_l2(out["agc"][i], golden["agc_sc"][i]) < TOL
+    if n_div == 0:
+        off = 1 if incl_clean else 0
+        assert np.array_equal(out["err"].astype(np.int64), errs[off:])
+        if golden is not None:
+            assert np.array_equal(out["err"].astype(np.int64)[np.asarray(iters)], golden["err"].astype(np.int64)[off:])
+    assert n_div <= max(1, n_frames // 2), "too many frames hit a sub-margin decision"
+    return out, frames
+
+
+@pytest.mark.parametrize("name", GOLDEN_4096)
+def test_golden_link_cases(engine, name):
+    g = load_golden(name)
+    cfg = cfg_from_golden(g)
+    csi = float(g["csi_eps"])
+    run_case(engine, cfg, float(g["snr_db"]), [int(v) for v in g["iters"]], list(g["seeds"]), int(g["n_frames"]),
+             bool(g["is_mcnc"]), bool(g["incl_clean"]), None if csi < 0 else csi, golden=g)
+
+
+@pytest.mark.parametrize("constel,pa,ibo", [(4, lo.PA_SOFT_LIMITER, -3.0), (16, lo.PA_SOFT_LIMITER, 2.0),
+                                            (256, lo.PA_SOFT_LIMITER, 0.0), (64, lo.PA_TOI, 20.0)])
+def test_other_constellations_and_pa(engine, constel, pa, ibo):
+    cfg = lo.LinkConfig(constel_size=constel, n_ant=4, pa_kind=pa, ibo_db=ibo, channel="two_path")
+    snr = float(lo.ebn0_to_snr(18.0, cfg.n_sub_carr, cfg.n_sub_carr, constel))
+    run_case(engine, cfg, snr, [0, 1, 2, 3], [5, 6, 7], 2, True, False, None)
+
+
+def test_single_antenna(engine):
+    cfg = lo.LinkConfig(n_ant=1, channel="los", ibo_db=1.0)
+    snr = float(lo.ebn0_to_snr(16.0, cfg.n_sub_carr, cfg.n_sub_carr, 64))
+    run_case(engine, cfg, snr, [0, 1, 2], [9, 8, 7], 2, True, False, None)
+    run_case(engine, cfg, snr, [0, 1, 2], [9, 8, 7], 2, False, False, None)
+
+
+def test_device_channel_generation_matches_oracle(engine):
+    """LOS / two-path channel generated on the device from injected receiver positions."""
+    for chan in ("los", "two_path"):
+        cfg = lo.LinkConfig(n_ant=8, channel=chan)
+        rng = np.random.default_rng(3)
+        pos = np.stack([lo.draw_rx_position(cfg, rng) for _ in range(3)])
+        engine.configure(n_ant=8, channel=chan)
+        out = engine.simulate(3, 0, 20.0, inject=dict(rx_pos=pos), dumps=("h_true", "rx_pos"))
+        for i in range(3):
+            h = lo.draw_channel(cfg, pos[i])[:, cfg.bins]
+            assert rel_l2(out["h_true"][i], h) < TOL
+
+
+def test_clean_run(engine):
+    g = load_golden("link_k8_two_path_mcnc_clean")
+    cfg = cfg_from_golden(g)
+    n = int(g["n_frames"])
+    snr = float(g["snr_db"])
+    # clean frames are the first n realisations of the streams
+    bit_rng, noise_rng, loc_rng = (np.random.default_rng(int(s)) for s in g["seeds"])
+    pos, tx, nz = [], [], []
+    for _ in range(n):
+        p = lo.draw_rx_position(cfg, loc_rng)
+        real = lo.make_realisation(cfg, lo.draw_channel(cfg, p))
+        pos.append(p)
+        tx.append(lo.bits_to_indices(bit_rng.choice((0, 1), cfg.n_bits_per_ofdm_sym), 6))
+        nz.append(lo.awgn_noise(noise_rng, cfg.n_fft, cfg.avg_symbol_power * real.hk_vk_noise_scaler, snr)[cfg.bins])
+    engine.configure(n_ant=cfg.n_ant, channel="two_path", ibo_db=cfg.ibo_db)
+    out = engine.simulate(n, 0, snr, incl_clean_run=True,
+                          inject=dict(clean_rx_pos=np.array(pos), clean_tx_idx=np.array(tx), clean_noise=np.array(nz)))
+    assert int(out["clean_err"][0]) == int(g["err"][0])
+
+
+def test_error_messages(engine):
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import MmimoError
+    with pytest.raises(MmimoError):
+        engine.configure(constel_size=32)
+    with pytest.raises(MmimoError):
+        engine.configure(n_fft=1024, n_sub_carr=512)
+    engine.configure(channel="injected")
+    with pytest.raises(MmimoError):
+        engine.simulate(1, 1, 10.0)
