@@ -4,6 +4,11 @@
 // i.e. the loop body of mp_model.py:208-222 with McncReceiver.receive (corrector.py:165-207) or
 // CncReceiver.receive (corrector.py:52-112) inlined.  The sum over antennas stays in registers: every
 // thread owns the same 8 data sub-carriers (native slot order, link_common.cuh) for every antenna.
+//
+// Precoder: either explicit rows V[k] (any precoder), or - the MRT case of antenna_array.py:170-171 -
+// derived on the fly from the channel-knowledge rows, v_k[s] = conj(h_k[s]) * sscale[s] with
+// sscale[s] = 1 / (64 ||h[:,s]||) written once per realisation by k_prep_realisation.  The derived form
+// halves the HBM traffic of the kernel (one 16 KB row per antenna and pass instead of two).
 #pragma once
 #include "link_common.cuh"
 
@@ -16,18 +21,20 @@ struct FrameScalars {   // written per frame by k_prep_realisation
     float noise_sigma_clean;
 };
 
+// one "array transmit + propagate" description (antenna_array.py:58-140 + channel.py:74-89)
+struct TxSide {
+    const float2* h_mac; long long h_mac_fs;   // [F][K][2048] channel applied to the transmitted signal
+    const float2* h_pre; long long h_pre_fs;   // [F][K][2048] channel knowledge the MRT precoder is derived from
+    const float2* v;     long long v_fs;       // [F][K][2048] explicit precoder (unscaled) or nullptr -> derive
+    const float* sscale; long long sscale_fs;  // [F][2048] symbol scale: 1/64 (explicit) or 1/(64 ||h||) (derived)
+    const float2* agc_inv; long long agc_fs;   // [F][2048] 1 / (64 * AGC)
+    int k;                                     // antennas
+};
+
 struct FrameArgs {
-    // pass 0: the real transmission (antenna_array.py:58-140, channel.py:74-89)
-    const float2* h_true; long long h_true_fs;      // [F][k_tx][2048] native slots; frame stride in float2
-    const float2* v_tx;   long long v_tx_fs;        // [F][k_tx][2048], pre-scaled by 1/64
-    int k_tx;
-    // passes 1..I: the receiver's model of the transmitter
-    const float2* h_loop; long long h_loop_fs;      // MCNC: channel knowledge; CNC: ones, stride 0
-    const float2* v_loop; long long v_loop_fs;      // MCNC: == v_tx; CNC: 1/64, stride 0
-    int k_loop;
-    const float2* agc_inv_rx;   long long agc_rx_fs;    // 1/(64*agc) applied to pass 0 (mp_model.py:214)
-    const float2* agc_inv_loop; long long agc_loop_fs;  // 1/(64*agc_corr_vec) (corrector.py:200) or 1/(64*alpha)
-    const FrameScalars* scal;   long long scal_fs;      // per frame (stride 1) or shared (stride 0)
+    TxSide tx;    // pass 0: the real transmission + mp_model.py:214
+    TxSide loop;  // passes 1..I: the receiver's model of the transmitter (MCNC: K antennas; CNC: 1, h = 1)
+    const FrameScalars* scal; long long scal_fs;  // per frame (stride 1) or shared (stride 0)
     float pa_p1;                                     // Rapp hardness
     int n_iter;                                      // I: detections 0..I are produced
     Qam qam;
@@ -35,6 +42,7 @@ struct FrameArgs {
     // inputs: injected or generated (Philox)
     const uint8_t* tx_idx;       // [F][2048] native slots, or nullptr
     const float2* noise;         // [F][2048] native slots (added before the AGC), or nullptr
+    const float2* rx_eq_in;      // [F][2048] equalised received signal: skips pass 0 (receiver-only use), or nullptr
     uint64_t seed; uint64_t frame_id0;
     // outputs
     uint8_t* det_out;            // [F][I+1][2048] native slots, or nullptr
@@ -47,15 +55,34 @@ struct FrameArgs {
 constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048 + 2048;
 constexpr int FRAME_SMEM_BYTES = FRAME_SMEM_FLOAT2 * 8 + 64 * 4;
 
+// packed PA (distortion.py:9-19 soft limiter, :102-113 Rapp, :202-211 third order)
+template <int KIND>
+__device__ __forceinline__ pf2 pa_apply_pk(pf2 xp, const float p0, const float sqrt_p0, const float p1) {
+    if (KIND == PA_NONE) return xp;
+    const float2 x = unpk(xp);
+    const float p = fmaf(x.x, x.x, x.y * x.y);
+    float g;
+    if (KIND == PA_SOFT_LIMITER) {
+        g = fminf(1.0f, sqrt_p0 * rsqrtf(p));  // p <= p0 -> exactly 1 (p = 0 -> inf -> 1)
+    } else if (KIND == PA_RAPP) {
+        const float r = __powf(p / p0, p1);
+        g = __powf(1.0f + r, -0.5f / p1);
+    } else {
+        g = 1.0f - p0 * p;
+    }
+    return pmul(xp, pbc(g));
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // One antenna: x (8 data slots, already precoded, 1/64 folded in) -> IFFT -> PA -> FFT; on return
 // x[0..3], x[12..15] hold the data bins of this thread (thread 0: x[4] = bin 1024).
 template <int PA>
-__device__ __forceinline__ void antenna_chain(float2 (&x)[16], float2* bufA, float2* bufB, const float2* tw2,
-                                              const Tw1& tw1, const int t, const float p0, const float sqrt_p0,
-                                              const float p1) {
+__device__ __forceinline__ void antenna_chain(pf2 (&x)[16], pf2* bufA, pf2* bufB, const float2* tw2, const Tw1& tw1,
+                                              const int t, const float p0, const float sqrt_p0, const float p1) {
     fft4096<+1, true, false>(x, bufA, bufB, tw2, tw1, t);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) x[j] = pa_apply<PA>(x[j], p0, sqrt_p0, p1);
+    for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA>(x[j], p0, sqrt_p0, p1);
     fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t);
 }
 
@@ -63,11 +90,11 @@ template <int PA>
 __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a, const float2* __restrict__ tw4096,
                                                                const float2* __restrict__ tw256) {
     extern __shared__ float2 smem[];
-    float2* bufA = smem;
-    float2* bufB = smem + 4096;
+    pf2* bufA = reinterpret_cast<pf2*>(smem);
+    pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
     float2* tw2 = smem + 8192;
-    float2* sym_s = tw2 + 256;     // current symbols, thread-private addresses jp*256+t
-    float2* rxeq_s = sym_s + 2048;  // equalised received signal, thread-private addresses
+    float2* symn_s = tw2 + 256;      // scaled current symbols, thread-private addresses jp*256+t
+    float2* rxeq_s = symn_s + 2048;  // equalised received signal, thread-private addresses
     unsigned int* err_s = reinterpret_cast<unsigned int*>(rxeq_s + 2048);
 
     const int t = threadIdx.x;
@@ -96,42 +123,69 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             txw[0] = r[0] & m4;
             txw[1] = r[1] & m4;
         }
-#pragma unroll
-        for (int jp = 0; jp < 8; ++jp)
-            sym_s[jp * 256 + t] = qam_symbol(a.qam, (txw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+        uint32_t curw[2] = {txw[0], txw[1]};  // symbols fed to the next array transmit
 
         for (int pass = 0; pass <= a.n_iter; ++pass) {
             const bool first = (pass == 0);
-            const int K = first ? a.k_tx : a.k_loop;
-            const float2* __restrict__ H = first ? a.h_true + f * a.h_true_fs : a.h_loop + f * a.h_loop_fs;
-            const float2* __restrict__ V = first ? a.v_tx + f * a.v_tx_fs : a.v_loop + f * a.v_loop_fs;
+            const TxSide& sd = first ? a.tx : a.loop;
+            const int K = (first && a.rx_eq_in) ? 0 : sd.k;  // receiver-only entry: no transmission in pass 0
+            const float2* __restrict__ Hm = sd.h_mac + f * sd.h_mac_fs;
+            const float2* __restrict__ Hp = sd.v ? sd.v + f * sd.v_fs : sd.h_pre + f * sd.h_pre_fs;
+            const bool explicit_v = sd.v != nullptr;
             const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
             const float sqrt_p0 = sqrtf(p0);
-            float2 acc[8];
+            {
+                const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs;
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) acc[jp] = make_float2(0.f, 0.f);
+                for (int jp = 0; jp < 8; ++jp) {
+                    const int p = jp * 256 + t;
+                    const float2 s = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float g = ss[p];
+                    symn_s[p] = make_float2(s.x * g, s.y * g);
+                }
+            }
+            pf2 acc[8];
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) acc[jp] = pk(0.f, 0.f);
 
             for (int k = 0; k < K; ++k) {
-                const float2* __restrict__ vk = V + (size_t)k * N_SC;
-                const float2* __restrict__ hk = H + (size_t)k * N_SC;
-                float2 x[16];
+                const float2* __restrict__ pr = Hp + (size_t)k * N_SC;
+                const float2* __restrict__ hk = Hm + (size_t)k * N_SC;
+                if (k + 2 < K) {  // pull the rows of antenna k+2 from HBM into L2 while this antenna computes
+                    const float2* qa = pr + 2 * N_SC;
+                    const float2* qb = hk + 2 * N_SC;
+                    if (t < 128) prefetch_l2(qa + t * 16);
+                    else if (qb != qa) prefetch_l2(qb + (t - 128) * 16);
+                }
+                pf2 x[16];
+                if (explicit_v) {
 #pragma unroll
-                for (int jp = 0; jp < 8; ++jp) x[jp_to_j(jp)] = cmul(sym_s[jp * 256 + t], __ldg(vk + jp * 256 + t));
+                    for (int jp = 0; jp < 8; ++jp) {
+                        const float2 s = symn_s[jp * 256 + t];
+                        x[jp_to_j(jp)] = pcmul(pk2(__ldg(pr + jp * 256 + t)), s.x, s.y);
+                    }
+                } else {
 #pragma unroll
-                for (int j = 4; j < 12; ++j) x[j] = make_float2(0.f, 0.f);
-                if (t == 0) { x[4] = x[0]; x[0] = make_float2(0.f, 0.f); }
+                    for (int jp = 0; jp < 8; ++jp) {  // conj(h) * (c + j s) = (h.x c + h.y s, h.x s - h.y c)
+                        const float2 s = symn_s[jp * 256 + t];
+                        const pf2 h = pk2(__ldg(pr + jp * 256 + t));
+                        x[jp_to_j(jp)] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));
+                    }
+                }
+#pragma unroll
+                for (int j = 4; j < 12; ++j) x[j] = pk(0.f, 0.f);
+                if (t == 0) { x[4] = x[0]; x[0] = pk(0.f, 0.f); }
                 antenna_chain<PA>(x, bufA, bufB, tw2, tw1, t, p0, sqrt_p0, a.pa_p1);
                 if (t == 0) x[0] = x[4];
 #pragma unroll
-                for (int jp = 0; jp < 8; ++jp) acc[jp] = cfma(__ldg(hk + jp * 256 + t), x[jp_to_j(jp)], acc[jp]);
+                for (int jp = 0; jp < 8; ++jp) acc[jp] = pcfma(x[jp_to_j(jp)], pk2(__ldg(hk + jp * 256 + t)), acc[jp]);
             }
 
             // ---- end of pass: equalise / estimate distortion / slice / count --------------------
             uint32_t detw[2] = {0u, 0u};
-            const float2* __restrict__ ai =
-                first ? a.agc_inv_rx + f * a.agc_rx_fs : a.agc_inv_loop + f * a.agc_loop_fs;
+            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
             float2 nz[8];
-            if (first) {
+            if (first && !a.rx_eq_in) {
                 if (a.noise) {
 #pragma unroll
                     for (int jp = 0; jp < 8; ++jp) nz[jp] = a.noise[(size_t)f * N_SC + jp * 256 + t];
@@ -152,22 +206,29 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
 #pragma unroll
             for (int jp = 0; jp < 8; ++jp) {
                 const int p = jp * 256 + t;
+                const float2 ac = unpk(acc[jp]);
                 float2 corr;
                 if (first) {
-                    const float2 r = make_float2(fmaf(64.f, nz[jp].x, acc[jp].x), fmaf(64.f, nz[jp].y, acc[jp].y));
-                    corr = cmul(r, ai[p]);
+                    if (a.rx_eq_in) {  // McncReceiver.receive / CncReceiver.receive entry (corrector.py:176,66)
+                        corr = a.rx_eq_in[(size_t)f * N_SC + p];
+                    } else {
+                        const float2 r = make_float2(fmaf(64.f, nz[jp].x, ac.x), fmaf(64.f, nz[jp].y, ac.y));
+                        corr = cmul(r, ai[p]);
+                    }
                     rxeq_s[p] = corr;
                     if (a.rx_eq_out) a.rx_eq_out[(size_t)f * N_SC + p] = corr;
                 } else {
-                    const float2 z = cmul(acc[jp], ai[p]);
-                    const float2 d = csub(z, sym_s[p]);  // distortion estimate, corrector.py:205
-                    corr = csub(rxeq_s[p], d);           // corrector.py:184
+                    const float2 z = cmul(ac, ai[p]);
+                    const float2 sy = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float2 d = csub(z, sy);   // distortion estimate, corrector.py:205
+                    corr = csub(rxeq_s[p], d);      // corrector.py:184
                 }
                 if (a.corr_out) a.corr_out[((size_t)f * (a.n_iter + 1) + pass) * N_SC + p] = corr;
                 const uint32_t idx = qam_detect(a.qam, corr);
-                sym_s[p] = qam_symbol(a.qam, idx);
                 detw[jp >> 2] |= idx << (8 * (jp & 3));
             }
+            curw[0] = detw[0];
+            curw[1] = detw[1];
             nerr = __popc(detw[0] ^ txw[0]) + __popc(detw[1] ^ txw[1]);
             nerr = __reduce_add_sync(0xffffffffu, nerr);
             if ((t & 31) == 0) atomicAdd(&err_s[pass], nerr);

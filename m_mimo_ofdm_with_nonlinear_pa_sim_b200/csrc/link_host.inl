@@ -40,7 +40,7 @@ struct RealisationIn {
 
 // channel -> (CSI error) -> MRT precoder + AGC for frames [c0, c0+n) of the request
 static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const RealisationIn& in, size_t c0, int n,
-                           float2** h_true_out, float2** h_loop_out) {
+                           float2** h_true_out, float2** h_loop_out, bool want_v) {
     const mmimo_link_config& cfg = c->cfg;
     const int K = cfg.n_ant;
     const size_t hN = (size_t)n * K * N_SC;
@@ -102,7 +102,8 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     PrepArgs pa{};
     pa.h_loop = h_loop; pa.h_fs = (long long)K * N_SC;
     pa.v_in = nullptr;
-    pa.v_out = c->v.as<float2>();
+    pa.v_out = want_v ? c->v.as<float2>() : nullptr;
+    pa.sscale = c->sscale.as<float>();
     pa.agc_inv = c->agc_inv.as<float2>();
     pa.hkvk_inv = c->hkvk_inv.as<float2>();
     pa.scal = c->scal.as<FrameScalars>();
@@ -133,15 +134,17 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
     const bool mcnc = cfg.receiver_kind == MMIMO_RX_MCNC;
     const bool sep_loop = rq->h_loop || rq->clean_h_loop || rq->csi_eps > 0.0;
     const bool want_det = rs && rs->det, want_corr = rs && rs->corr, want_rxeq = rs && rs->rx_eq;
+    const bool want_v = rs && rs->v;
     // chunking: per-frame scratch bytes
-    size_t per_frame = (size_t)K * N_SC * 8 * (sep_loop ? 3 : 2) + (size_t)N_SC * (8 * 4 + 1) + 64 + (size_t)K * 4;
+    size_t per_frame = (size_t)K * N_SC * 8 * ((sep_loop ? 2 : 1) + (want_v ? 1 : 0)) + (size_t)N_SC * (8 * 4 + 4 + 1) + 64 + (size_t)K * 4;
     if (want_det) per_frame += (size_t)(I + 1) * N_SC;
     if (want_corr) per_frame += (size_t)(I + 1) * N_SC * 8;
     size_t chunk = std::max<size_t>(1, c->scratch_budget / per_frame);
     chunk = std::min<size_t>(chunk, (size_t)rq->n_frames);
     chunk = std::min<size_t>(chunk, 8192);
     const size_t hB = chunk * K * N_SC * 8;
-    if (c->h_true.reserve(hB) || c->v.reserve(hB) || c->agc_inv.reserve(chunk * N_SC * 8) ||
+    if (c->h_true.reserve(hB) || (want_v && c->v.reserve(hB)) || c->sscale.reserve(chunk * N_SC * 4) ||
+        c->agc_inv.reserve(chunk * N_SC * 8) ||
         c->hkvk_inv.reserve(chunk * N_SC * 8) || c->scal.reserve(chunk * sizeof(FrameScalars)) ||
         c->alpha.reserve(chunk * K * 4) || c->rx_pos.reserve(chunk * 24) || c->tx_idx.reserve(chunk * N_SC) ||
         c->noise.reserve(chunk * N_SC * 8) || c->err.reserve(chunk * (I + 1) * 4) || c->rx_eq.reserve(chunk * N_SC * 8))
@@ -149,10 +152,10 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
     if (want_det && c->det.reserve(chunk * (I + 1) * N_SC)) return 1;
     if (want_corr && c->corr.reserve(chunk * (I + 1) * N_SC * 8)) return 1;
     if (!mcnc) {
-        if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 8) || c->cnc_agc_inv.reserve(N_SC * 8)) return 1;
+        if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 4) || c->cnc_agc_inv.reserve(N_SC * 8)) return 1;
         const double alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
         k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_ones.as<float2>(), make_float2(1.f, 0.f), N_SC);
-        k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float2>(), make_float2(1.f / 64.f, 0.f), N_SC);
+        k_fill_f<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float>(), 1.f / 64.f, N_SC);
         k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_agc_inv.as<float2>(), make_float2((float)(1.0 / (64.0 * alpha)), 0.f), N_SC);
         c->launches += 3;
     }
@@ -163,10 +166,10 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         float2 *h_true = nullptr, *h_loop = nullptr;
         if (rq->incl_clean_run) {
             RealisationIn in{rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
-            if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop)) return 1;
+            if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, false)) return 1;
             CleanArgs ca{};
             ca.h_true = h_true; ca.h_fs = (long long)K * N_SC;
-            ca.v = c->v.as<float2>(); ca.v_fs = (long long)K * N_SC;
+            ca.h_pre = h_loop; ca.sscale = c->sscale.as<float>();
             ca.hkvk_inv = c->hkvk_inv.as<float2>();
             ca.scal = c->scal.as<FrameScalars>();
             ca.n_ant = K; ca.n_frames = n;
@@ -191,23 +194,26 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             if (rs && rs->clean_det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->clean_det + c0 * N_SC, n)) return 1;
         }
         RealisationIn in{rq->rx_pos, rq->h_true, rq->h_loop, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
-        if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop)) return 1;
+        if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, want_v)) return 1;
 
         FrameArgs fa{};
-        fa.h_true = h_true; fa.h_true_fs = (long long)K * N_SC;
-        fa.v_tx = c->v.as<float2>(); fa.v_tx_fs = (long long)K * N_SC;
-        fa.k_tx = K;
-        fa.agc_inv_rx = c->agc_inv.as<float2>(); fa.agc_rx_fs = N_SC;
+        const long long hfs = (long long)K * N_SC;
+        fa.tx.h_mac = h_true; fa.tx.h_mac_fs = hfs;
+        fa.tx.h_pre = h_loop; fa.tx.h_pre_fs = hfs;
+        fa.tx.v = nullptr; fa.tx.v_fs = 0;
+        fa.tx.sscale = c->sscale.as<float>(); fa.tx.sscale_fs = N_SC;
+        fa.tx.agc_inv = c->agc_inv.as<float2>(); fa.tx.agc_fs = N_SC;
+        fa.tx.k = K;
         if (mcnc) {
-            fa.h_loop = h_loop; fa.h_loop_fs = (long long)K * N_SC;
-            fa.v_loop = fa.v_tx; fa.v_loop_fs = fa.v_tx_fs;
-            fa.k_loop = K;
-            fa.agc_inv_loop = fa.agc_inv_rx; fa.agc_loop_fs = N_SC;
-        } else {
-            fa.h_loop = c->cnc_ones.as<float2>(); fa.h_loop_fs = 0;
-            fa.v_loop = c->cnc_v.as<float2>(); fa.v_loop_fs = 0;
-            fa.k_loop = 1;
-            fa.agc_inv_loop = c->cnc_agc_inv.as<float2>(); fa.agc_loop_fs = 0;
+            fa.loop = fa.tx;
+            fa.loop.h_mac = h_loop;
+        } else {  // single-antenna model of the transmitter, corrector.py:52-112: h = v = 1, estimate / alpha
+            fa.loop.h_mac = c->cnc_ones.as<float2>(); fa.loop.h_mac_fs = 0;
+            fa.loop.h_pre = c->cnc_ones.as<float2>(); fa.loop.h_pre_fs = 0;
+            fa.loop.v = nullptr; fa.loop.v_fs = 0;
+            fa.loop.sscale = c->cnc_v.as<float>(); fa.loop.sscale_fs = 0;
+            fa.loop.agc_inv = c->cnc_agc_inv.as<float2>(); fa.loop.agc_fs = 0;
+            fa.loop.k = 1;
         }
         fa.scal = c->scal.as<FrameScalars>(); fa.scal_fs = 1;
         fa.pa_p1 = (float)cfg.p_hardness;
@@ -247,11 +253,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             if (rs->rx_eq && download_native<float2>(c, c->rx_eq.as<float2>(), reinterpret_cast<float2*>(rs->rx_eq) + c0 * N_SC, n)) return 1;
             if (rs->h_true && download_native<float2>(c, h_true, reinterpret_cast<float2*>(rs->h_true) + c0 * K * N_SC, (size_t)n * K)) return 1;
             if (rs->v) {
-                if (c->s_a.reserve((size_t)n * K * N_SC * 8)) return 1;
-                CK(cudaMemcpyAsync(c->s_a.p, c->v.p, (size_t)n * K * N_SC * 8, cudaMemcpyDeviceToDevice, c->stream));
-                k_scale<<<nblk((size_t)n * K * N_SC), 256, 0, c->stream>>>(c->s_a.as<float2>(), 64.f, (size_t)n * K * N_SC);
-                c->launches++;
-                if (download_native<float2>(c, c->s_a.as<float2>(), reinterpret_cast<float2*>(rs->v) + c0 * K * N_SC, (size_t)n * K)) return 1;
+                if (download_native<float2>(c, c->v.as<float2>(), reinterpret_cast<float2*>(rs->v) + c0 * K * N_SC, (size_t)n * K)) return 1;
             }
             if (rs->agc) {
                 if (c->s_a.reserve((size_t)n * N_SC * 8)) return 1;

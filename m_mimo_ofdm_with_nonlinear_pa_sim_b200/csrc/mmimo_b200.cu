@@ -64,7 +64,7 @@ struct mmimo_ctx {
     // tables
     DevBuf tw4096, tw256, freq_slot, freq_bin, tx_pos;
     // per-chunk scratch
-    DevBuf h_true, h_loop, v, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
+    DevBuf h_true, h_loop, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // stage-op scratch
@@ -117,6 +117,10 @@ __global__ void k_agc_from_inv(const float2* __restrict__ inv, float2* __restric
 __global__ void k_scale(float2* __restrict__ x, float s, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) { x[i].x *= s; x[i].y *= s; }
+}
+__global__ void k_fill_f(float* __restrict__ x, float v, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] = v;
 }
 __global__ void k_fill_c(float2* __restrict__ x, float2 v, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -171,7 +175,7 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->v, &c->agc_inv,
+    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
                      &c->s_a, &c->s_b, &c->s_c, &c->s_d};

@@ -89,7 +89,8 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
 struct PrepArgs {
     const float2* h_loop; long long h_fs;  // channel knowledge [F][K][2048]
     const float2* v_in;                    // optional externally supplied precoder [F][K][2048] (unscaled)
-    float2* v_out;                         // [F][K][2048] precoder / 64
+    float2* v_out;                         // [F][K][2048] precoder (unscaled) or nullptr
+    float* sscale;                         // [F][2048] symbol scale of the frame kernel: 1/(64 ||h||) (MRT) or 1/64
     float2* agc_inv;                       // [F][2048]  1 / (64 * sum_k alpha_k h_k v_k)
     float2* hkvk_inv;                      // [F][2048]  1 / (sum_k h_k v_k)        (clean run, no FFT scale)
     FrameScalars* scal;                    // [F]
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
     const int f = blockIdx.x, t = threadIdx.x, K = a.n_ant;
     const float2* __restrict__ H = a.h_loop + f * a.h_fs;
     const float2* __restrict__ Vin = a.v_in ? a.v_in + (size_t)f * K * N_SC : nullptr;
-    float2* Vout = a.v_out + (size_t)f * K * N_SC;
+    float2* Vout = a.v_out ? a.v_out + (size_t)f * K * N_SC : nullptr;
 
     float ninv[8];
     if (!Vin) {
@@ -139,6 +140,8 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
 #pragma unroll
         for (int jp = 0; jp < 8; ++jp) ninv[jp] = 1.0f / sqrtf(nrm[jp]);
     }
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) a.sscale[(size_t)f * N_SC + jp * 256 + t] = Vin ? 0.015625f : ninv[jp] * 0.015625f;
     // precoder out + per-antenna power
     for (int k = 0; k < K; ++k) {
         float pw = 0.f;
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
                 v = make_float2(h.x * ninv[jp], -h.y * ninv[jp]);
             }
             pw = fmaf(v.x, v.x, fmaf(v.y, v.y, pw));
-            Vout[(size_t)k * N_SC + p] = make_float2(v.x * 0.015625f, v.y * 0.015625f);
+            if (Vout) Vout[(size_t)k * N_SC + p] = v;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) pw += __shfl_xor_sync(0xffffffffu, pw, o);
@@ -227,7 +230,8 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
 // ---------------------------------------------------------------------------------------------
 struct CleanArgs {
     const float2* h_true; long long h_fs;
-    const float2* v;      long long v_fs;   // pre-scaled by 1/64 (as written by k_prep_realisation)
+    const float2* h_pre;                    // channel knowledge: v_k = conj(h_pre_k) * sscale (MRT, antenna_array.py:170-171)
+    const float* sscale;                    // [F][2048] 1/(64 ||h_pre||)
     const float2* hkvk_inv;                 // [F][2048]
     const FrameScalars* scal;
     int n_ant, n_frames;
@@ -261,10 +265,15 @@ __global__ void __launch_bounds__(256) k_clean_frame(const CleanArgs a) {
 #pragma unroll
     for (int jp = 0; jp < 8; ++jp) g[jp] = make_float2(0.f, 0.f);
     const float2* __restrict__ H = a.h_true + f * a.h_fs;
-    const float2* __restrict__ V = a.v + f * a.v_fs;
+    const float2* __restrict__ HP = a.h_pre + f * a.h_fs;
     for (int k = 0; k < a.n_ant; ++k) {
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) g[jp] = cfma(H[(size_t)k * N_SC + jp * 256 + t], V[(size_t)k * N_SC + jp * 256 + t], g[jp]);
+        for (int jp = 0; jp < 8; ++jp) g[jp] = cadd(g[jp], cmulc(H[(size_t)k * N_SC + jp * 256 + t], HP[(size_t)k * N_SC + jp * 256 + t]));
+    }
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        const float ssc = a.sscale[(size_t)f * N_SC + jp * 256 + t];
+        g[jp].x *= ssc; g[jp].y *= ssc;
     }
     float2 nz[8];
     if (a.noise) {
