@@ -33,6 +33,9 @@ typedef struct mmimo_ctx mmimo_ctx;
 enum { MMIMO_PA_NONE = 0, MMIMO_PA_SOFT_LIMITER = 1, MMIMO_PA_RAPP = 2, MMIMO_PA_TOI = 3 };
 enum { MMIMO_CHAN_LOS = 0, MMIMO_CHAN_TWO_PATH = 1, MMIMO_CHAN_RAYLEIGH = 2, MMIMO_CHAN_INJECTED = 3 };
 enum { MMIMO_RX_CNC = 0, MMIMO_RX_MCNC = 1 };
+/* request flags: injected `noise` / `clean_noise` hold the raw standard-normal pairs of noise.py:66 and the device
+ * applies the per-frame 0.5 * noise_std of noise.py:64 (which depends on the realisation's AGC vector) */
+enum { MMIMO_REQ_NOISE_UNIT = 1 };
 
 /* Static description of one link: the objects main_mp_miso_mcnc_ber_vs_ebn0.py:64-104 builds. */
 typedef struct mmimo_link_config {
@@ -60,8 +63,8 @@ typedef struct mmimo_link_config {
 typedef struct mmimo_sim_request {
     int32_t n_frames;
     int32_t n_iter;            /* max(cnc_n_iter_lst): detections after 0..n_iter iterations are counted */
-    int32_t incl_clean_run;    /* also run the "no distortion" frames of mp_model.py:136-175 */
-    int32_t reserved;
+    int32_t incl_clean_run;    /* 1: also run the "no distortion" frames of mp_model.py:136-175; 2: run ONLY those */
+    int32_t flags;             /* MMIMO_REQ_* */
     double snr_db;             /* Link.set_snr  mp_model.py:243 */
     double csi_eps;            /* Link(csi_epsylon): > 0 draws h_loop on the device (mp_model.py:264-284); ignored
                                   when h_loop is injected */
@@ -79,6 +82,11 @@ typedef struct mmimo_sim_request {
     const float* clean_h_loop;
     const uint8_t* clean_tx_idx;
     const float* clean_noise;
+    /* CSI-error draws (mp_model.py:272): c64 [n_frames][n_ant][n_sub_carr] unit-variance pairs exactly as
+     * rng.standard_normal((n_sub_carr, 2)) yields them per antenna; the device applies
+     * 0.5 * sqrt(2 * mean|h_k|^2) * csi_eps.  NULL = Philox.  Ignored unless csi_eps > 0 and h_loop == NULL. */
+    const float* csi_noise;
+    const float* clean_csi_noise;
 } mmimo_sim_request;
 
 typedef struct mmimo_sim_result {
@@ -97,9 +105,11 @@ typedef struct mmimo_sim_result {
     float* alpha;              /* [n_frames][n_ant] per-antenna Bussgang alpha (mp_model.py:315-317) */
     double* rx_pos;            /* [n_frames][3] */
     uint8_t* clean_det;        /* [n_frames][n_sub_carr] */
+    uint32_t* clean_err_per_frame; /* [n_frames] */
 } mmimo_sim_result;
 
 /* context ------------------------------------------------------------------------------------ */
+int mmimo_device_count(void);                   /* number of CUDA devices visible to this process, < 0 on error */
 int mmimo_create(mmimo_ctx** out, int device);
 void mmimo_destroy(mmimo_ctx* ctx);
 const char* mmimo_last_error(void);
@@ -128,6 +138,88 @@ int mmimo_counters_to_device(mmimo_ctx* ctx, void* dst_dev, int clear);
 /* number of kernels launched by this context so far (bench.py "gpu_launches") */
 uint64_t mmimo_launch_count(mmimo_ctx* ctx);
 
+
+/* ---- stage-level (unfused) operations: one call per reference building-block method ------------------
+ * Used by the drop-in classes (m_mimo_ofdm_with_nonlinear_pa_sim_b200/dropin/), where a script drives the
+ * blocks one by one instead of through Link.simulate.  Any n_fft = 2^m (8..8192), any even n_sub_carr < n_fft.
+ * Frequency-domain arrays: FFT-bin order; per-sub-carrier arrays: data order; bits: one byte (0/1) per bit,
+ * MSB of each symbol first (utilities.py:18-67). */
+typedef struct mmimo_modem_desc {
+    int32_t constel_size;      /* QamModem(constel_size)  modulation.py:223 */
+    int32_t n_fft;             /* OfdmQamModem.n_fft      modulation.py:296 */
+    int32_t n_sub_carr;
+    int32_t cp_len;
+    double constel_scale;      /* 1, or alpha after Modem.correct_constellation (modulation.py:167-176) */
+} mmimo_modem_desc;
+
+typedef struct mmimo_pa_desc {
+    int32_t kind;              /* MMIMO_PA_* */
+    int32_t reserved;
+    double p0;                 /* SoftLimiter/Rapp .sat_pow (distortion.py:37,131) ; ThirdOrderNonLin .cubic_dist_coeff (:228) */
+    double p1;                 /* Rapp .p_hardness */
+} mmimo_pa_desc;
+
+enum { MMIMO_TX_SKIP_DIST = 1, MMIMO_TX_TIME_DOMAIN = 2, MMIMO_TX_PER_USER = 4 };
+enum { MMIMO_PREC_PHASE = 0, MMIMO_PREC_MRT = 1, MMIMO_PREC_ZF = 2 };
+
+/* utilities.to_freq_domain / to_time_domain (utilities.py:311-339), modulation._tx/_rx_ofdm_symbol transforms:
+ * `rows` orthonormal transforms of length n; `skip` leading samples of every input row are dropped (cyclic prefix
+ * removal), `cp` trailing output samples are repeated in front of every output row (cyclic prefix insertion). */
+int mmimo_fft(mmimo_ctx* ctx, int inverse, int n, int rows, int skip, int cp, const float* in, float* out);
+/* SoftLimiter/Rapp/ThirdOrderNonLin.process (distortion.py:91-98, :191-198, :281) on n complex samples */
+int mmimo_pa_process(mmimo_ctx* ctx, const mmimo_pa_desc* pa, size_t n, const float* in, float* out);
+/* modulation.modulate (modulation.py:13-25): bits -> n_sym constellation points */
+int mmimo_qam_map(mmimo_ctx* ctx, const mmimo_modem_desc* m, size_t n_sym, const uint8_t* bits, float* symbols);
+/* Modem.symbol_detection (:138-146) / demodulate (:63-77): nearest points (symbols, may be NULL) and their bits (may be NULL) */
+int mmimo_qam_detect(mmimo_ctx* ctx, const mmimo_modem_desc* m, size_t n_sym, const float* in, float* symbols, uint8_t* bits);
+/* AntennaArray.transmit (antenna_array.py:58-140) = Transceiver.transmit (transceiver.py:98-174) for n_ant antennas that
+ * share one modem description and one PA (pa == NULL: no impairment).
+ *   bits     [n_users][n_sub_carr * log2(constel)]
+ *   precoder c64 [n_ant][n_users][n_sub_carr] (AntennaArray.get_precoding_mat layout) or NULL
+ *   out      c64 [G][n_ant][n_out], G = n_users with MMIMO_TX_PER_USER else 1, n_out = n_fft or n_fft + cp_len (TIME_DOMAIN)
+ *   out_clean same shape: the undistorted signal (return_both), or NULL */
+int mmimo_array_transmit(mmimo_ctx* ctx, const mmimo_modem_desc* m, const mmimo_pa_desc* pa, int n_ant, int n_users,
+                         const uint8_t* bits, const float* precoder, int flags, float* out, float* out_clean);
+/* OfdmQamModem.demodulate (modulation.py:384-396): time-domain symbol with cyclic prefix -> data sub-carrier symbols
+ * (may be NULL) and hard-decision bits (may be NULL) */
+int mmimo_ofdm_demodulate(mmimo_ctx* ctx, const mmimo_modem_desc* m, const float* td, float* symbols, uint8_t* bits);
+/* Miso*Fd.propagate (channel.py:74-89): x, h c64 [n_ant][n]; out [n] (sum_signals) or [n_ant][n] */
+int mmimo_propagate(mmimo_ctx* ctx, int n_ant, int n, const float* x, const float* h, int sum_signals, float* out);
+/* Awgn.process (noise.py:45-83): out = in + scale * unit_noise; the draw itself stays with the caller's numpy Generator */
+int mmimo_awgn_add(mmimo_ctx* ctx, size_t n, const float* in, const float* unit_noise, double scale, float* out);
+/* utilities.count_mismatched_bits (utilities.py:94-104) */
+int mmimo_count_mismatched_bits(mmimo_ctx* ctx, size_t n, const uint8_t* a, const uint8_t* b, uint64_t* out);
+/* MisoLosFd / MisoTwoPathFd.calc_channel_mat (channel.py:35-72, :116-167): kind = MMIMO_CHAN_LOS | MMIMO_CHAN_TWO_PATH;
+ * h_out c64 [n_ant][n_fft] */
+int mmimo_channel_geometric(mmimo_ctx* ctx, int kind, int n_ant, int n_fft, const double* tx_pos, const double* tx_gain_db,
+                            double rx_gain_db, const double* rx_pos, const double* freqs, int skip_attenuation, float* h_out);
+/* MisoRayleighFd (channel.py:225-250, :262-275): free-space attenuation matrix times the caller's IID coefficients
+ * (coeffs == NULL: the attenuation matrix itself) */
+int mmimo_channel_fspl(mmimo_ctx* ctx, int n_ant, int n_fft, const double* tx_pos, const double* tx_gain_db, double rx_gain_db,
+                       const double* rx_pos, const double* freqs, const float* coeffs, float* h_out);
+/* MisoRandomPathsFd (channel.py:330-344, :358-384) from the drawn departure angles and delays */
+int mmimo_channel_random_paths(mmimo_ctx* ctx, int n_ant, int n_fft, const double* tx_pos, const double* freqs, int n_paths,
+                               const double* angles, const double* taus, float* h_out);
+/* AntennaArray.set_precoding_matrix (antenna_array.py:142-311): h c64 [n_users][n_ant][n_fft] -> v c64 [n_ant][n_users][n_sub_carr]
+ * (sep_carriers: [n_ant][n_sub_carr], antenna_array.py:275-305) */
+int mmimo_precoding(mmimo_ctx* ctx, int mode, int sep_carriers, int n_users, int n_ant, int n_fft, int n_sub_carr, const float* h,
+                    float* v);
+/* McncReceiver.__init__/update_agc (corrector.py:126-163, :209-245; MU :348-403, :453-489) and Link.recalculate_agc
+ * (mp_model.py:290-329).  alpha_fixed != NULL: every antenna uses *alpha_fixed (third-order PA), else calc_alpha of the
+ * per-antenna IBO.  Outputs (any may be NULL): agc_nfft / hkvk_nfft c64 [n_fft] (ones off the data sub-carriers),
+ * scalers[2] = mean|sum_k alpha_k h_k v_k|^2, mean|sum_k h_k v_k|^2, vk_pow[n_ant], alpha[n_ant] */
+int mmimo_agc(mmimo_ctx* ctx, int n_ant, int n_users, int usr_idx, int n_fft, int n_sub_carr, const float* h, const float* v,
+              double ibo_db, const double* alpha_fixed, float* agc_nfft, float* hkvk_nfft, double* scalers, double* vk_pow,
+              float* alpha);
+/* CncReceiver.receive (corrector.py:52-112) / CncMuReceiver.receive (:288-345, other_usr_symbols != NULL).
+ * in_sig_fd c64 [n_fft]; det_bits [n_iter+1][n_sub_carr*log2(constel)] and corr c64 [n_iter+1][n_sub_carr] (either may be NULL) */
+int mmimo_cnc_receive(mmimo_ctx* ctx, const mmimo_modem_desc* m, const mmimo_pa_desc* pa, double alpha, int n_iter,
+                      const float* in_sig_fd, const float* other_usr_symbols, uint8_t* det_bits, float* corr);
+/* McncReceiver.receive (corrector.py:165-207) / McncMuReceiver.receive (:405-451, other_usr_bits [n_users-1][bits] in user order).
+ * h c64 [n_ant][n_fft] (the receiver's channel knowledge), v [n_ant][n_users][n_sub_carr], agc_nfft c64 [n_fft] */
+int mmimo_mcnc_receive(mmimo_ctx* ctx, const mmimo_modem_desc* m, const mmimo_pa_desc* pa, int n_ant, int n_users, int usr_idx,
+                       const float* h, const float* v, const float* agc_nfft, int n_iter, const float* in_sig_fd,
+                       const uint8_t* other_usr_bits, uint8_t* det_bits, float* corr);
 
 /* measurement helpers (bench.py): per-kernel CUDA-event timing on the context's stream.
  * kinds: 0 channel generation, 1 realisation prep (precoder/AGC), 2 fused frame kernel, 3 other */

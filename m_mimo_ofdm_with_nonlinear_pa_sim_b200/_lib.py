@@ -20,17 +20,17 @@ class LinkConfig(C.Structure):
 
 
 class SimRequest(C.Structure):
-    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("incl_clean_run", C.c_int32), ("reserved", C.c_int32),
+    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("incl_clean_run", C.c_int32), ("flags", C.c_int32),
                 ("snr_db", C.c_double), ("csi_eps", C.c_double), ("seed", C.c_uint64), ("frame_id0", C.c_uint64),
                 ("rx_pos", c_d_p), ("h_true", c_f_p), ("h_loop", c_f_p), ("tx_idx", c_u8_p), ("noise", c_f_p),
                 ("clean_rx_pos", c_d_p), ("clean_h_true", c_f_p), ("clean_h_loop", c_f_p), ("clean_tx_idx", c_u8_p),
-                ("clean_noise", c_f_p)]
+                ("clean_noise", c_f_p), ("csi_noise", c_f_p), ("clean_csi_noise", c_f_p)]
 
 
 class SimResult(C.Structure):
     _fields_ = [("err", c_u64_p), ("clean_err", c_u64_p), ("bits_per_frame", C.c_uint64), ("det", c_u8_p),
                 ("err_per_frame", c_u32_p), ("rx_eq", c_f_p), ("corr", c_f_p), ("h_true", c_f_p), ("v", c_f_p),
-                ("agc", c_f_p), ("pa_p0", c_f_p), ("alpha", c_f_p), ("rx_pos", c_d_p), ("clean_det", c_u8_p)]
+                ("agc", c_f_p), ("pa_p0", c_f_p), ("alpha", c_f_p), ("rx_pos", c_d_p), ("clean_det", c_u8_p), ("clean_err_per_frame", c_u32_p)]
 
 
 class MmimoError(RuntimeError):
@@ -40,10 +40,15 @@ class MmimoError(RuntimeError):
 _LIB = None
 
 # every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
-EXPORTS = ["mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
+EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
            "mmimo_set_stream", "mmimo_counters_to_device",
            "mmimo_configure", "mmimo_set_ibo", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
-           "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak"]
+           "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
+           # stage-level operations (see _stage_abi.STAGE_EXPORTS)
+           "mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_array_transmit",
+           "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
+           "mmimo_channel_geometric", "mmimo_channel_fspl", "mmimo_channel_random_paths", "mmimo_precoding",
+           "mmimo_agc", "mmimo_cnc_receive", "mmimo_mcnc_receive"]
 
 
 def lib_path() -> str:
@@ -65,6 +70,7 @@ def load(build_if_missing: bool = True):
     if not os.path.isfile(path):
         raise MmimoError("libmmimo_b200.so not found at %s - run `python __graft_entry__.py build`" % path)
     lib = C.CDLL(path)
+    lib.mmimo_device_count.restype = C.c_int
     lib.mmimo_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
     lib.mmimo_create.restype = C.c_int
     lib.mmimo_destroy.argtypes = [C.c_void_p]
@@ -92,11 +98,8 @@ def load(build_if_missing: bool = True):
 
 
 def _bind_stage_ops(lib):
-    """argtypes of the stage-level entry points (filled in by _stage_abi when present)."""
-    try:
-        from . import _stage_abi
-    except ImportError:
-        return
+    """argtypes of the stage-level entry points."""
+    from . import _stage_abi
     _stage_abi.bind(lib)
 
 

@@ -42,6 +42,7 @@ struct FrameArgs {
     // inputs: injected or generated (Philox)
     const uint8_t* tx_idx;       // [F][2048] native slots, or nullptr
     const float2* noise;         // [F][2048] native slots (added before the AGC), or nullptr
+    int noise_unit;              // injected noise holds unit normals: scale by the frame's noise_sigma (noise.py:64-66)
     const float2* rx_eq_in;      // [F][2048] equalised received signal: skips pass 0 (receiver-only use), or nullptr
     uint64_t seed; uint64_t frame_id0;
     // outputs
@@ -188,7 +189,12 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             if (first && !a.rx_eq_in) {
                 if (a.noise) {
 #pragma unroll
-                    for (int jp = 0; jp < 8; ++jp) nz[jp] = a.noise[(size_t)f * N_SC + jp * 256 + t];
+                    const float ns = a.noise_unit ? sc.noise_sigma : 1.0f;
+#pragma unroll
+                    for (int jp = 0; jp < 8; ++jp) {
+                        const float2 u = a.noise[(size_t)f * N_SC + jp * 256 + t];
+                        nz[jp] = make_float2(u.x * ns, u.y * ns);
+                    }
                 } else {
                     const uint64_t fid = a.frame_id0 + f;
 #pragma unroll

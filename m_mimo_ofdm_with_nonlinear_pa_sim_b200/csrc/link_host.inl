@@ -35,6 +35,7 @@ struct RealisationIn {
     const double* rx_pos;
     const float* h_true;
     const float* h_loop;
+    const float* csi_noise;
     uint32_t pos_stream, ray_stream, csi_stream;
 };
 
@@ -94,6 +95,11 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         if (c->h_loop.reserve(hN * 8)) return 1;
         h_loop = c->h_loop.as<float2>();
         CsiArgs xa{};
+        if (in.csi_noise) {
+            if (c->csi_nz.reserve(hN * 8)) return 1;
+            if (upload_native<float2>(c, reinterpret_cast<const float2*>(in.csi_noise) + c0 * K * N_SC, c->csi_nz.as<float2>(), (size_t)n * K)) return 1;
+            xa.noise_in = c->csi_nz.as<float2>();
+        }
         xa.h_in = h_true; xa.h_out = h_loop; xa.eps = (float)rq->csi_eps; xa.scale = (float)sqrt(1.0 - rq->csi_eps * rq->csi_eps);
         xa.seed = rq->seed; xa.frame_id0 = rq->frame_id0 + c0; xa.stream = in.csi_stream; xa.n_ant = K;
         k_csi_error<<<dim3(K, n), 256, 0, c->stream>>>(xa);
@@ -136,7 +142,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
     const bool want_det = rs && rs->det, want_corr = rs && rs->corr, want_rxeq = rs && rs->rx_eq;
     const bool want_v = rs && rs->v;
     // chunking: per-frame scratch bytes
-    size_t per_frame = (size_t)K * N_SC * 8 * ((sep_loop ? 2 : 1) + (want_v ? 1 : 0)) + (size_t)N_SC * (8 * 4 + 4 + 1) + 64 + (size_t)K * 4;
+    size_t per_frame = (size_t)K * N_SC * 8 * ((sep_loop ? 2 : 1) + (want_v ? 1 : 0) + ((rq->csi_noise || rq->clean_csi_noise) ? 1 : 0)) + (size_t)N_SC * (8 * 4 + 4 + 1) + 64 + (size_t)K * 4;
     if (want_det) per_frame += (size_t)(I + 1) * N_SC;
     if (want_corr) per_frame += (size_t)(I + 1) * N_SC * 8;
     size_t chunk = std::max<size_t>(1, c->scratch_budget / per_frame);
@@ -165,7 +171,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
         float2 *h_true = nullptr, *h_loop = nullptr;
         if (rq->incl_clean_run) {
-            RealisationIn in{rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
+            RealisationIn in{rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, rq->clean_csi_noise, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
             if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, false)) return 1;
             CleanArgs ca{};
             ca.h_true = h_true; ca.h_fs = (long long)K * N_SC;
@@ -183,17 +189,22 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
                 if (upload_native<float2>(c, reinterpret_cast<const float2*>(rq->clean_noise) + c0 * N_SC, c->noise.as<float2>(), n)) return 1;
                 ca.noise = c->noise.as<float2>();
             }
+            ca.noise_unit = (rq->flags & MMIMO_REQ_NOISE_UNIT) ? 1 : 0;
             ca.seed = rq->seed; ca.frame_id0 = rq->frame_id0 + c0;
+            if (rs && rs->clean_det && c->det.reserve((size_t)chunk * (I + 1) * N_SC)) return 1;
             ca.det_out = (rs && rs->clean_det) ? c->det.as<uint8_t>() : nullptr;
-            if (ca.det_out && c->det.reserve((size_t)chunk * (I + 1) * N_SC)) return 1;
-            ca.det_out = (rs && rs->clean_det) ? c->det.as<uint8_t>() : nullptr;
-            ca.err_out = nullptr;
+            ca.err_out = (rs && rs->clean_err_per_frame) ? c->err.as<uint32_t>() : nullptr;
             ca.err_total = counters + 64;
             k_clean_frame<<<n, 256, 0, c->stream>>>(ca);
             c->launches++;
             if (rs && rs->clean_det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->clean_det + c0 * N_SC, n)) return 1;
+            if (rs && rs->clean_err_per_frame) {
+                CK(cudaMemcpyAsync(rs->clean_err_per_frame + c0, c->err.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+                CK(cudaStreamSynchronize(c->stream));  // c->err is rewritten by the distorted frames of this chunk
+            }
         }
-        RealisationIn in{rq->rx_pos, rq->h_true, rq->h_loop, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
+        if (rq->incl_clean_run == 2) continue;  // clean frames only
+        RealisationIn in{rq->rx_pos, rq->h_true, rq->h_loop, rq->csi_noise, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
         if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, want_v)) return 1;
 
         FrameArgs fa{};
@@ -229,6 +240,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             if (upload_native<float2>(c, reinterpret_cast<const float2*>(rq->noise) + c0 * N_SC, c->noise.as<float2>(), n)) return 1;
             fa.noise = c->noise.as<float2>();
         }
+        fa.noise_unit = (rq->flags & MMIMO_REQ_NOISE_UNIT) ? 1 : 0;
         fa.seed = rq->seed; fa.frame_id0 = rq->frame_id0 + c0;
         fa.det_out = want_det ? c->det.as<uint8_t>() : nullptr;
         fa.rx_eq_out = want_rxeq ? c->rx_eq.as<float2>() : nullptr;

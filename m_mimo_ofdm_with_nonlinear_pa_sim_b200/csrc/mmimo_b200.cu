@@ -64,7 +64,7 @@ struct mmimo_ctx {
     // tables
     DevBuf tw4096, tw256, freq_slot, freq_bin, tx_pos;
     // per-chunk scratch
-    DevBuf h_true, h_loop, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
+    DevBuf h_true, h_loop, csi_nz, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // stage-op scratch
@@ -132,6 +132,12 @@ static inline unsigned nblk(size_t n, int bs = 256) { return (unsigned)((n + bs 
 extern "C" const char* mmimo_last_error(void) { return g_err.c_str(); }
 extern "C" const char* mmimo_version(void) { return "mmimo_b200 0.1 (sm_100a)"; }
 
+extern "C" int mmimo_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { fail("cudaGetDeviceCount failed"); return -1; }
+    return n;
+}
+
 extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     if (!out) return fail("mmimo_create: out is NULL");
     *out = nullptr;
@@ -175,7 +181,7 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->v, &c->sscale, &c->agc_inv,
+    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
                      &c->s_a, &c->s_b, &c->s_c, &c->s_d};

@@ -236,7 +236,7 @@ struct CleanArgs {
     const FrameScalars* scal;
     int n_ant, n_frames;
     Qam qam;
-    const uint8_t* tx_idx; const float2* noise;
+    const uint8_t* tx_idx; const float2* noise; int noise_unit;
     uint64_t seed, frame_id0;
     uint8_t* det_out;            // [F][2048] or nullptr
     uint32_t* err_out;           // [F] or nullptr
@@ -278,7 +278,11 @@ __global__ void __launch_bounds__(256) k_clean_frame(const CleanArgs a) {
     float2 nz[8];
     if (a.noise) {
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) nz[jp] = a.noise[(size_t)f * N_SC + jp * 256 + t];
+        for (int jp = 0; jp < 8; ++jp) {
+            const float2 u = a.noise[(size_t)f * N_SC + jp * 256 + t];
+            const float ns = a.noise_unit ? sc.noise_sigma_clean : 1.0f;
+            nz[jp] = make_float2(u.x * ns, u.y * ns);
+        }
     } else {
         const uint64_t fid = a.frame_id0 + f;
 #pragma unroll
@@ -348,6 +352,7 @@ __global__ void __launch_bounds__(256) k_gen_rayleigh(const RayleighArgs a) {
 // k_csi_error: mp_model.py:264-284, h_hat = sqrt(1-eps^2) h + eps CN(0, mean_s |h_k[s]|^2) per antenna.
 // ---------------------------------------------------------------------------------------------
 struct CsiArgs {
+    const float2* noise_in;  // [F][K][2048] injected unit normals (native slots) or nullptr -> Philox
     const float2* h_in; float2* h_out; float eps, scale;
     uint64_t seed, frame_id0; uint32_t stream; int n_ant;
 };
@@ -366,6 +371,15 @@ __global__ void __launch_bounds__(256) k_csi_error(const CsiArgs a) {
     }
     pw = block_sum_256(pw, red_s, t) / N_SC;
     const float sig = a.eps * (float)sqrt(0.5 * pw);
+    if (a.noise_in) {
+        const float2* nz = a.noise_in + ((size_t)f * a.n_ant + k) * N_SC;
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) {
+            const float2 g = nz[jp * 256 + t];
+            out[jp * 256 + t] = make_float2(fmaf(a.scale, h[jp].x, sig * g.x), fmaf(a.scale, h[jp].y, sig * g.y));
+        }
+        return;
+    }
     const uint64_t fid = a.frame_id0 + f;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {

@@ -1,5 +1,506 @@
-// Stage-level kernels behind the drop-in building-block classes (filled in below).
+// Stage-level (unfused) kernels behind the drop-in building-block classes: one kernel per reference
+// method, any n_fft = 2^m (8..8192) and any even n_sub_carr < n_fft.  All arrays use the REFERENCE's
+// orders: frequency-domain vectors in FFT-bin order (DC at 0), per-sub-carrier vectors in data order
+// ("negative half then positive half", modulation.py:266-267).  These kernels are HBM-bound
+// (K x n_fft complex64 in, the same out); the Monte-Carlo hot loop does not use them - it runs the
+// fused frame kernel (frame_kernel.cuh).
 #pragma once
 #include "prep_kernels.cuh"
-namespace mmimo {}
-static int stage_kernels_init() { return 0; }
+
+namespace mmimo {
+
+// data-sub-carrier index of FFT bin n, or -1 (DC / guard band)
+__host__ __device__ __forceinline__ int sc_of_bin(int n, int n_fft, int n_sc) {
+    const int h = n_sc >> 1;
+    if (n >= 1 && n <= h) return h + n - 1;
+    if (n >= n_fft - h) return n - (n_fft - h);
+    return -1;
+}
+__host__ __device__ __forceinline__ int bin_of_sc(int s, int n_fft, int n_sc) {
+    const int h = n_sc >> 1;
+    return s < h ? n_fft - h + s : s - h + 1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// bits (one byte per bit, MSB first) -> symbol values.  modulation.py:13-25 + utilities.py:54-67
+// ---------------------------------------------------------------------------------------------
+__global__ void k_bits_to_idx(const uint8_t* __restrict__ bits, uint8_t* __restrict__ idx, size_t n_sym, int bps) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sym) return;
+    uint32_t v = 0;
+    for (int b = 0; b < bps; ++b) v = (v << 1) | (bits[i * bps + b] & 1u);
+    idx[i] = (uint8_t)v;
+}
+// symbol values -> bits.  utilities.py:18-51
+__global__ void k_idx_to_bits(const uint8_t* __restrict__ idx, uint8_t* __restrict__ bits, size_t n_sym, int bps) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sym) return;
+    const uint32_t v = idx[i];
+    for (int b = 0; b < bps; ++b) bits[i * bps + b] = (uint8_t)((v >> (bps - 1 - b)) & 1u);
+}
+// symbol values -> constellation points (scale = alpha of a corrected constellation, modulation.py:167-176)
+__global__ void k_idx_to_symbols(const uint8_t* __restrict__ idx, float2* __restrict__ sym, size_t n_sym, Qam q, float scale) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sym) return;
+    const float2 s = qam_symbol(q, idx[i]);
+    sym[i] = make_float2(s.x * scale, s.y * scale);
+}
+// Modem.symbol_detection / demodulate (modulation.py:138-146, :63-77): nearest point of the scaled table
+__global__ void k_detect(const float2* __restrict__ in, uint8_t* __restrict__ idx, float2* __restrict__ sym, size_t n_sym,
+                         Qam q, float scale) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sym) return;
+    const float2 r = in[i];
+    const float inv = 1.0f / scale;
+    const uint32_t v = qam_detect(q, make_float2(r.x * inv, r.y * inv));
+    if (idx) idx[i] = (uint8_t)v;
+    if (sym) {
+        const float2 s = qam_symbol(q, v);
+        sym[i] = make_float2(s.x * scale, s.y * scale);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// OfdmQamModem.modulate up to the IFFT input (modulation.py:346-382 + :264-267): symbol values of
+// every user -> precode -> sum over users -> place on the n_fft grid, for every antenna.
+//   idx   [U][n_sc]          symbol values
+//   v     [K][U][n_sc]       precoder in AntennaArray.get_precoding_mat layout, or nullptr (no precoding)
+//   extra [n_sc]             optional additive term (CncMuReceiver: the other user's symbols, corrector.py:322)
+//   grid  [G][K][n_fft]      G = U when per_user (sum_usr_signals=False), else 1
+// ---------------------------------------------------------------------------------------------
+struct MapArgs {
+    const uint8_t* idx; const float2* v; const float2* extra; float2* grid;
+    int n_users, n_ant, n_fft, n_sc, per_user;
+    Qam q; float scale;       // constellation scale
+    float w_self, w_extra;    // weights of the mapped symbols and of `extra`
+};
+__global__ void k_map_precode(const MapArgs a) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= a.n_fft) return;
+    const int k = blockIdx.y, g = blockIdx.z;
+    const int s = sc_of_bin(n, a.n_fft, a.n_sc);
+    float2 acc = make_float2(0.f, 0.f);
+    if (s >= 0) {
+        const int u0 = a.per_user ? g : 0, u1 = a.per_user ? g + 1 : a.n_users;
+        for (int u = u0; u < u1; ++u) {
+            float2 sym = qam_symbol(a.q, a.idx[(size_t)u * a.n_sc + s]);
+            sym.x *= a.scale * a.w_self; sym.y *= a.scale * a.w_self;
+            if (a.v) sym = cmul(sym, a.v[((size_t)k * a.n_users + u) * a.n_sc + s]);
+            acc = cadd(acc, sym);
+        }
+        if (a.extra) {
+            const float2 e = a.extra[s];
+            acc.x = fmaf(a.w_extra, e.x, acc.x); acc.y = fmaf(a.w_extra, e.y, acc.y);
+        }
+    }
+    a.grid[((size_t)g * a.n_ant + k) * a.n_fft + n] = acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batched orthonormal FFT / IFFT, one CTA per row.  torch.fft.fft/ifft(norm="ortho") call sites
+// utilities.py:329,339, modulation.py:270,290, corrector.py:93,98.
+// n == 4096: the register/shared-memory radix-16 transform of fft4096.cuh.
+// otherwise: radix-2 Stockham autosort in shared memory (n <= 8192).
+// `skip` input samples are dropped in front of each input row (cyclic prefix removal, utilities.py:323);
+// `cp` samples are prepended to each output row (modulation.py:273).
+// ---------------------------------------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(FFT_THREADS) k_fft4096_rows(const float2* __restrict__ in, float2* __restrict__ out,
+                                                              const float2* __restrict__ tw4096, const float2* __restrict__ tw256,
+                                                              int skip, int cp) {
+    extern __shared__ float2 smem[];
+    pf2* bufA = reinterpret_cast<pf2*>(smem);
+    pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
+    float2* tw2 = smem + 8192;
+    const int t = threadIdx.x;
+    tw2[t] = tw256[t];
+    Tw1 tw1;
+    load_tw1(tw1, tw4096, t);
+    __syncthreads();
+    const float2* src = in + (size_t)blockIdx.x * (4096 + skip) + skip;
+    float2* dst = out + (size_t)blockIdx.x * (4096 + cp) + cp;
+    pf2 x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = pk2(src[t + 256 * j]);
+    fft4096<S, false, false>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const float2 y = unpk(x[j]);
+        const float2 o = make_float2(y.x * 0.015625f, y.y * 0.015625f);
+        const int n = t + 256 * j;
+        dst[n] = o;
+        if (n >= 4096 - cp) dst[n - 4096] = o;  // cyclic prefix = last cp samples
+    }
+}
+
+template <int S>
+__global__ void __launch_bounds__(256) k_fft_generic_rows(const float2* __restrict__ in, float2* __restrict__ out, int n,
+                                                          int log2n, int skip, int cp) {
+    extern __shared__ float2 smem[];
+    float2* a = smem;
+    float2* b = smem + n;
+    const float2* src = in + (size_t)blockIdx.x * (n + skip) + skip;
+    float2* dst = out + (size_t)blockIdx.x * (n + cp) + cp;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) a[i] = src[i];
+    __syncthreads();
+    // Stockham autosort, decimation in frequency: sub-transform length nn halves, stride s doubles
+    const int half = n >> 1;
+    for (int st = 0, nn = n, s = 1; st < log2n; ++st, nn >>= 1, s <<= 1) {
+        const int m = nn >> 1;
+        for (int i = threadIdx.x; i < half; i += blockDim.x) {
+            const int p = i / s, q = i - p * s;  // p in [0,m), q in [0,s)
+            float sn, cs;
+            sincospif((float)(S * 2 * p) / (float)nn, &sn, &cs);  // exp(S 2 pi i p / nn), argument exact in fp32
+            const float2 c0 = a[q + s * p];
+            const float2 c1 = a[q + s * (p + m)];
+            b[q + s * (2 * p)] = cadd(c0, c1);
+            b[q + s * (2 * p + 1)] = cmul(csub(c0, c1), make_float2(cs, sn));
+        }
+        __syncthreads();
+        float2* tmp = a; a = b; b = tmp;
+    }
+    const float sc = rsqrtf((float)n);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float2 y = a[i];
+        const float2 o = make_float2(y.x * sc, y.y * sc);
+        dst[i] = o;
+        if (i >= n - cp) dst[i - n] = o;
+    }
+}
+
+// prepend the cyclic prefix to every row (modulation.py:273): out[r] = in[r][n-cp:] ++ in[r]
+__global__ void k_add_cp(const float2* __restrict__ in, float2* __restrict__ out, int n, int cp) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+    if (i >= n + cp) return;
+    out[(size_t)r * (n + cp) + i] = in[(size_t)r * n + (i < cp ? n - cp + i : i - cp)];
+}
+
+// ---------------------------------------------------------------------------------------------
+// PA models on a flat array.  distortion.py:9-19, :102-113, :202-211
+// ---------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void k_pa(const float2* __restrict__ in, float2* __restrict__ out, size_t n, float p0, float p1) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = pa_apply<KIND>(in[i], p0, sqrtf(p0), p1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Miso*Fd.propagate (channel.py:74-89): Y = X .* H, optionally summed over antennas.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_propagate(const float2* __restrict__ x, const float2* __restrict__ h, float2* __restrict__ out, int n_ant,
+                            int n, int sum) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (sum) {
+        float2 acc = make_float2(0.f, 0.f);
+        for (int k = 0; k < n_ant; ++k) acc = cfma(x[(size_t)k * n + i], h[(size_t)k * n + i], acc);
+        out[i] = acc;
+    } else {
+        const int k = blockIdx.y;
+        out[(size_t)k * n + i] = cmul(x[(size_t)k * n + i], h[(size_t)k * n + i]);
+    }
+}
+
+// out = in + scale * noise   (Awgn.process, noise.py:64-83: the draw itself comes from the caller's numpy Generator)
+__global__ void k_axpy_c(const float2* __restrict__ in, const float2* __restrict__ nz, float2* __restrict__ out, float sr,
+                         size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = make_float2(fmaf(sr, nz[i].x, in[i].x), fmaf(sr, nz[i].y, in[i].y));
+}
+
+// utilities.count_mismatched_bits (utilities.py:94-104)
+__global__ void k_count_mismatch(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, size_t n,
+                                 unsigned long long* __restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int c = 0;
+    for (; i < n; i += (size_t)gridDim.x * blockDim.x) c += (a[i] != b[i]);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Channels on the full n_fft grid (channel.py:35-72 LOS, :116-167 two-path), per-antenna gains.
+// ---------------------------------------------------------------------------------------------
+struct ChanFullArgs {
+    const double* tx_pos;   // [K][3]
+    const double* tx_gain;  // [K] dB
+    const double* freqs;    // [n_fft]
+    double rx[3]; double rx_gain_db;
+    int kind, skip_attenuation, n_fft;
+    float2* h_out;          // [K][n_fft]
+};
+__global__ void k_channel_full(const ChanFullArgs a) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+    if (n >= a.n_fft) return;
+    const double tz = a.tx_pos[k * 3 + 2];
+    const double dx = a.tx_pos[k * 3 + 0] - a.rx[0], dy = a.tx_pos[k * 3 + 1] - a.rx[1], dz = tz - a.rx[2];
+    const double gain = sqrt(pow(10.0, (a.tx_gain[k] + a.rx_gain_db) / 10.0));
+    const double f = a.freqs[n];
+    float2 h = path_coeff(sqrt(dx * dx + dy * dy + dz * dz), f, gain, a.skip_attenuation);
+    if (a.kind == 1) {
+        const double el = atan((tz + a.rx[2]) / sqrt(dx * dx + dy * dy));
+        const double sn = sin(el);
+        const float2 g = path_coeff(tz / sn + a.rx[2] / sn, f, gain, a.skip_attenuation);
+        h.x -= g.x; h.y -= g.y;
+    }
+    a.h_out[(size_t)k * a.n_fft + n] = h;
+}
+// free-space attenuation matrix (channel.py:225-227) and its product with injected IID coefficients (:244-250)
+__global__ void k_fspl_apply(const ChanFullArgs a, const float2* __restrict__ coeffs) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+    if (n >= a.n_fft) return;
+    const double dx = a.tx_pos[k * 3 + 0] - a.rx[0], dy = a.tx_pos[k * 3 + 1] - a.rx[1], dz = a.tx_pos[k * 3 + 2] - a.rx[2];
+    const double gain = sqrt(pow(10.0, (a.tx_gain[k] + a.rx_gain_db) / 10.0));
+    const float att = (float)(gain * C_LIGHT / (4.0 * 3.14159265358979323846 * sqrt(dx * dx + dy * dy + dz * dz) * a.freqs[n]));
+    const float2 c = coeffs ? coeffs[(size_t)k * a.n_fft + n] : make_float2(1.f, 0.f);
+    a.h_out[(size_t)k * a.n_fft + n] = make_float2(c.x * att, c.y * att);
+}
+// MisoRandomPathsFd (channel.py:330-344), literally: exp(-2j f (tau_p + delta_k sin(phi_p / c))) summed over paths
+struct RandPathArgs {
+    const double* tx_pos; const double* freqs; const double* angles; const double* taus;
+    int n_paths, n_fft; float2* h_out;
+};
+__global__ void k_channel_random_paths(const RandPathArgs a) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+    if (n >= a.n_fft) return;
+    const double dx = a.tx_pos[k * 3 + 0] - a.tx_pos[0], dy = a.tx_pos[k * 3 + 1] - a.tx_pos[1], dz = a.tx_pos[k * 3 + 2] - a.tx_pos[2];
+    const double delta = sqrt(dx * dx + dy * dy + dz * dz);
+    const double f = a.freqs[n];
+    double re = 0.0, im = 0.0;
+    for (int p = 0; p < a.n_paths; ++p) {
+        const double arg = -2.0 * f * (a.taus[p] + delta * sin(a.angles[p] / C_LIGHT));
+        double s, c;
+        sincos(arg, &s, &c);  // |arg| ~ 7e3 rad: double-precision range reduction
+        re += c; im += s;
+    }
+    const double sc = 1.0 / sqrt((double)a.n_paths);
+    a.h_out[(size_t)k * a.n_fft + n] = make_float2((float)(re * sc), (float)(im * sc));
+}
+
+// ---------------------------------------------------------------------------------------------
+// AntennaArray.set_precoding_matrix (antenna_array.py:142-311).  h [U][K][n_fft] -> v [K][U][n_sc].
+// One thread per data sub-carrier; antennas looped (coalesced across sub-carriers).
+// ---------------------------------------------------------------------------------------------
+enum PrecMode : int { PREC_PHASE = 0, PREC_MRT = 1, PREC_ZF = 2 };
+constexpr int MAX_USERS = 8;
+struct PrecArgs {
+    const float2* h; float2* v;
+    int n_users, n_ant, n_fft, n_sc, mode;
+    int sep_carriers;  // user u owns the u-th block of n_sc / U sub-carriers (:275-305); output is [K][1][n_sc]
+};
+__global__ void k_precoding(const PrecArgs a) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= a.n_sc) return;
+    const int bin = bin_of_sc(s, a.n_fft, a.n_sc);
+    const int U = a.n_users, K = a.n_ant;
+    const size_t us = (size_t)K * a.n_fft;
+    if (a.sep_carriers) {
+        const int u = s / (a.n_sc / U);
+        const float2* hu = a.h + (size_t)u * us + bin;
+        float nrm = 0.f;
+        for (int k = 0; k < K; ++k) { const float2 h = hu[(size_t)k * a.n_fft]; nrm = fmaf(h.x, h.x, fmaf(h.y, h.y, nrm)); }
+        const float inv = rsqrtf(nrm);
+        for (int k = 0; k < K; ++k) {
+            const float2 h = hu[(size_t)k * a.n_fft];
+            float2 o;
+            if (a.mode == PREC_MRT) o = make_float2(h.x * inv, -h.y * inv);
+            else { const float m = rsqrtf(fmaf(h.x, h.x, h.y * h.y)); o = make_float2(h.x * m, -h.y * m); }
+            a.v[(size_t)k * a.n_sc + s] = o;
+        }
+        return;
+    }
+    if (a.mode == PREC_PHASE) {  // exp(1j angle(conj h)), :178 / :259-264
+        for (int u = 0; u < U; ++u)
+            for (int k = 0; k < K; ++k) {
+                const float2 h = a.h[(size_t)u * us + (size_t)k * a.n_fft + bin];
+                const float m = rsqrtf(fmaf(h.x, h.x, h.y * h.y));
+                a.v[((size_t)k * U + u) * a.n_sc + s] = make_float2(h.x * m, -h.y * m);
+            }
+        return;
+    }
+    if (a.mode == PREC_MRT) {  // conj(h_u) / sqrt(sum_u sum_k |h_u|^2), :170-171 / :202-220
+        float nrm = 0.f;
+        for (int u = 0; u < U; ++u)
+            for (int k = 0; k < K; ++k) {
+                const float2 h = a.h[(size_t)u * us + (size_t)k * a.n_fft + bin];
+                nrm = fmaf(h.x, h.x, fmaf(h.y, h.y, nrm));
+            }
+        const float inv = 1.0f / sqrtf(nrm);
+        for (int u = 0; u < U; ++u)
+            for (int k = 0; k < K; ++k) {
+                const float2 h = a.h[(size_t)u * us + (size_t)k * a.n_fft + bin];
+                a.v[((size_t)k * U + u) * a.n_sc + s] = make_float2(h.x * inv, -h.y * inv);
+            }
+        return;
+    }
+    // zero forcing (:222-257): T = [h_1 .. h_U] (K x U); V = sqrt(K-U) conj(T) inv(T^T conj(T)); unit Frobenius norm.
+    // Gram matrix and its inverse in double: the users' LOS channels can be close to collinear.
+    double gr[MAX_USERS][MAX_USERS], gi[MAX_USERS][MAX_USERS], ir[MAX_USERS][MAX_USERS], ii[MAX_USERS][MAX_USERS];
+    for (int p = 0; p < U; ++p)
+        for (int q = 0; q < U; ++q) {
+            double sr = 0.0, si = 0.0;
+            for (int k = 0; k < K; ++k) {
+                const float2 hp = a.h[(size_t)p * us + (size_t)k * a.n_fft + bin];
+                const float2 hq = a.h[(size_t)q * us + (size_t)k * a.n_fft + bin];
+                sr += (double)hp.x * hq.x + (double)hp.y * hq.y;  // h_p * conj(h_q)
+                si += (double)hp.y * hq.x - (double)hp.x * hq.y;
+            }
+            gr[p][q] = sr; gi[p][q] = si;
+            ir[p][q] = (p == q) ? 1.0 : 0.0; ii[p][q] = 0.0;
+        }
+    for (int c = 0; c < U; ++c) {  // Gauss-Jordan with partial pivoting
+        int piv = c; double best = gr[c][c] * gr[c][c] + gi[c][c] * gi[c][c];
+        for (int r = c + 1; r < U; ++r) {
+            const double m = gr[r][c] * gr[r][c] + gi[r][c] * gi[r][c];
+            if (m > best) { best = m; piv = r; }
+        }
+        if (piv != c)
+            for (int q = 0; q < U; ++q) {
+                double t;
+                t = gr[c][q]; gr[c][q] = gr[piv][q]; gr[piv][q] = t;
+                t = gi[c][q]; gi[c][q] = gi[piv][q]; gi[piv][q] = t;
+                t = ir[c][q]; ir[c][q] = ir[piv][q]; ir[piv][q] = t;
+                t = ii[c][q]; ii[c][q] = ii[piv][q]; ii[piv][q] = t;
+            }
+        const double pr = gr[c][c] / best, pi = -gi[c][c] / best;  // 1 / pivot
+        for (int q = 0; q < U; ++q) {
+            double xr = gr[c][q], xi = gi[c][q];
+            gr[c][q] = xr * pr - xi * pi; gi[c][q] = xr * pi + xi * pr;
+            xr = ir[c][q]; xi = ii[c][q];
+            ir[c][q] = xr * pr - xi * pi; ii[c][q] = xr * pi + xi * pr;
+        }
+        for (int r = 0; r < U; ++r) {
+            if (r == c) continue;
+            const double fr = gr[r][c], fi = gi[r][c];
+            for (int q = 0; q < U; ++q) {
+                gr[r][q] -= fr * gr[c][q] - fi * gi[c][q]; gi[r][q] -= fr * gi[c][q] + fi * gr[c][q];
+                ir[r][q] -= fr * ir[c][q] - fi * ii[c][q]; ii[r][q] -= fr * ii[c][q] + fi * ir[c][q];
+            }
+        }
+    }
+    double fro = 0.0;
+    for (int pass = 0; pass < 2; ++pass) {
+        const double sc = pass ? 1.0 / sqrt(fro) : 0.0;
+        for (int k = 0; k < K; ++k)
+            for (int u = 0; u < U; ++u) {
+                double vr = 0.0, vi = 0.0;
+                for (int p = 0; p < U; ++p) {  // conj(h_p[k]) * Ginv[p][u]
+                    const float2 hp = a.h[(size_t)p * us + (size_t)k * a.n_fft + bin];
+                    vr += (double)hp.x * ir[p][u] + (double)hp.y * ii[p][u];
+                    vi += (double)hp.x * ii[p][u] - (double)hp.y * ir[p][u];
+                }
+                if (!pass) fro += vr * vr + vi * vi;
+                else a.v[((size_t)k * U + u) * a.n_sc + s] = make_float2((float)(vr * sc), (float)(vi * sc));
+            }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// AGC / alpha bookkeeping: corrector.py:126-163,209-245 (+MU :348-403) and mp_model.py:290-329.
+//   k_vk_pow : vk_pow[k] = sum_{u,s} |v[k][u][s]|^2 ; alpha[k] = calc_alpha(10 log10(ibo_lin n_sc / (vk_pow K)))
+//   k_agc    : agc[bin(s)] = sum_k alpha_k h_k v_{k,usr}, hkvk likewise with alpha = 1; 1 elsewhere
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_vk_pow(const float2* __restrict__ v, double* __restrict__ vk_pow, float* __restrict__ alpha,
+                                                int n_ant, int row_len, double ibo_lin, int n_sc, double alpha_fixed, int use_fixed) {
+    __shared__ double red_s[8];
+    const int k = blockIdx.x, t = threadIdx.x;
+    double s = 0.0;
+    for (int i = t; i < row_len; i += 256) {
+        const float2 x = v[(size_t)k * row_len + i];
+        s += (double)x.x * x.x + (double)x.y * x.y;
+    }
+    s = block_sum_256(s, red_s, t);
+    if (t == 0) {
+        vk_pow[k] = s;
+        double al = alpha_fixed;
+        if (!use_fixed) {
+            const double g2 = ibo_lin * (double)n_sc / (s * (double)n_ant);
+            const double g = sqrt(g2);
+            al = 1.0 - exp(-g2) + (1.7724538509055160273 * g * 0.5) * erfc(g);
+        }
+        alpha[k] = (float)al;
+    }
+}
+struct AgcArgs {
+    const float2* h; const float2* v; const float* alpha;
+    float2* agc_nfft; float2* hkvk_nfft;  // [n_fft] each
+    double* scalers;                       // [2] mean |agc|^2, mean |hkvk|^2 over data sub-carriers (atomicAdd)
+    int n_ant, n_users, usr, n_fft, n_sc;
+};
+__global__ void k_agc(const AgcArgs a) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    double p_agc = 0.0, p_hv = 0.0;
+    if (n < a.n_fft) {
+        const int s = sc_of_bin(n, a.n_fft, a.n_sc);
+        float2 agc = make_float2(1.f, 0.f), hv = make_float2(1.f, 0.f);
+        if (s >= 0) {
+            agc = hv = make_float2(0.f, 0.f);
+            for (int k = 0; k < a.n_ant; ++k) {
+                const float2 m = cmul(a.h[(size_t)k * a.n_fft + n], a.v[((size_t)k * a.n_users + a.usr) * a.n_sc + s]);
+                hv = cadd(hv, m);
+                const float al = a.alpha[k];
+                agc = make_float2(fmaf(al, m.x, agc.x), fmaf(al, m.y, agc.y));
+            }
+            p_agc = (double)agc.x * agc.x + (double)agc.y * agc.y;
+            p_hv = (double)hv.x * hv.x + (double)hv.y * hv.y;
+        }
+        a.agc_nfft[n] = agc;
+        a.hkvk_nfft[n] = hv;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        p_agc += __shfl_xor_sync(0xffffffffu, p_agc, o);
+        p_hv += __shfl_xor_sync(0xffffffffu, p_hv, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&a.scalers[0], p_agc / a.n_sc);
+        atomicAdd(&a.scalers[1], p_hv / a.n_sc);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Receiver iteration pieces (corrector.py:71-110, :181-205, MU :305-343, :422-449)
+// ---------------------------------------------------------------------------------------------
+// take the data sub-carriers of a full-band vector (corrector.py:66,176)
+__global__ void k_take_sc(const float2* __restrict__ fd, float2* __restrict__ sc, int n_fft, int n_sc) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n_sc) sc[s] = fd[bin_of_sc(s, n_fft, n_sc)];
+}
+// corr = rx - dist_est ; detect
+__global__ void k_rx_correct_detect(const float2* __restrict__ rx_sc, const float2* __restrict__ dist_est, float2* __restrict__ corr_out,
+                                    uint8_t* __restrict__ idx_out, int n_sc, Qam q, float scale) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_sc) return;
+    float2 c = rx_sc[s];
+    if (dist_est) c = csub(c, dist_est[s]);
+    if (corr_out) corr_out[s] = c;
+    const float inv = 1.0f / scale;
+    idx_out[s] = (uint8_t)qam_detect(q, make_float2(c.x * inv, c.y * inv));
+}
+// dist_est[s] = (sum_k X[k][bin] H[k][bin]) / agc[bin] - symbol   (MCNC, K antennas; CNC: K = 1, h = nullptr, agc = alpha)
+__global__ void k_rx_estimate(const float2* __restrict__ x, const float2* __restrict__ h, const float2* __restrict__ agc_nfft,
+                              float inv_alpha, const uint8_t* __restrict__ idx, float2* __restrict__ dist_est, int n_ant, int n_fft,
+                              int n_sc, Qam q, float scale) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_sc) return;
+    const int bin = bin_of_sc(s, n_fft, n_sc);
+    float2 acc = make_float2(0.f, 0.f);
+    if (h) {
+        for (int k = 0; k < n_ant; ++k) acc = cfma(x[(size_t)k * n_fft + bin], h[(size_t)k * n_fft + bin], acc);
+        const float2 g = agc_nfft[bin];
+        const float d = 1.0f / fmaf(g.x, g.x, g.y * g.y);
+        acc = cmulc(acc, g);
+        acc.x *= d; acc.y *= d;
+    } else {
+        acc = x[bin];
+        acc.x *= inv_alpha; acc.y *= inv_alpha;
+    }
+    const float2 sy = qam_symbol(q, idx[s]);
+    dist_est[s] = make_float2(acc.x - sy.x * scale, acc.y - sy.y * scale);
+}
+
+}  // namespace mmimo
+
+static int stage_kernels_init();

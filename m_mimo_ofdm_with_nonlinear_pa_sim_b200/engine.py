@@ -50,6 +50,12 @@ class LinkEngine:
 
     def __init__(self, device: int = 0):
         self._lib = _lib.load()
+        if device < 0:  # spread worker processes over the visible GPUs
+            import os
+            n = self._lib.mmimo_device_count()
+            if n <= 0:
+                raise _lib.MmimoError("no CUDA device visible: %s" % self._lib.mmimo_last_error().decode("utf-8", "replace"))
+            device = os.getpid() % n
         h = C.c_void_p()
         _lib.check(self._lib, self._lib.mmimo_create(C.byref(h), int(device)))
         self._h = h
@@ -102,16 +108,18 @@ class LinkEngine:
         self.cfg["ibo_db"] = float(ibo_db)
 
     # ------------------------------------------------------------------------------------------
-    def _request(self, n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject):
+    def _request(self, n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject, noise_unit=False):
         K = self.cfg["n_ant"]
         rq = _lib.SimRequest()
-        rq.n_frames, rq.n_iter, rq.incl_clean_run = int(n_frames), int(n_iter), int(bool(incl_clean_run))
+        rq.n_frames, rq.n_iter = int(n_frames), int(n_iter)
+        rq.incl_clean_run = 2 if incl_clean_run == "only" else int(bool(incl_clean_run))
+        rq.flags = 1 if noise_unit else 0
         rq.snr_db, rq.csi_eps = float(snr_db), float(csi_eps or 0.0)
         rq.seed, rq.frame_id0 = int(seed) & (2 ** 64 - 1), int(frame_id0)
         keep = []
         inject = inject or {}
         unknown = set(inject) - {"rx_pos", "h_true", "h_loop", "tx_idx", "noise", "clean_rx_pos", "clean_h_true",
-                                 "clean_h_loop", "clean_tx_idx", "clean_noise"}
+                                 "clean_h_loop", "clean_tx_idx", "clean_noise", "csi_noise", "clean_csi_noise"}
         if unknown:
             raise ValueError("unknown injected inputs: %s" % sorted(unknown))
         for pre in ("", "clean_"):
@@ -120,7 +128,7 @@ class LinkEngine:
                 a = np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(n_frames, 3))
                 keep.append(a)
                 setattr(rq, pre + "rx_pos", _ptr(a, C.c_double))
-            for name in ("h_true", "h_loop"):
+            for name in ("h_true", "h_loop", "csi_noise"):
                 v = inject.get(pre + name)
                 if v is not None:
                     a = _c64(v, (n_frames, K, N_SC))
@@ -139,14 +147,16 @@ class LinkEngine:
         return rq, keep
 
     def simulate(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
-                 inject=None, dumps=()):
+                 inject=None, dumps=(), noise_unit=False):
         """Run `n_frames` frames; returns dict(err=[n_iter+1], bits=..., clean_err, + requested dumps).
 
-        dumps: any of det, err_per_frame, rx_eq, corr, h_true, v, agc, pa_p0, alpha, rx_pos, clean_det."""
+        dumps: any of det, err_per_frame, rx_eq, corr, h_true, v, agc, pa_p0, alpha, rx_pos, clean_det,
+        clean_err_per_frame.  incl_clean_run: False | True | "only" (just the no-distortion frames).
+        noise_unit: injected noise arrays hold raw standard normals, scaled on the device (noise.py:64-66)."""
         if self.cfg is None:
             raise _lib.MmimoError("LinkEngine.configure() has not been called")
         K, I = self.cfg["n_ant"], int(n_iter)
-        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject)
+        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject, noise_unit)
         rs = _lib.SimResult()
         out = {"err": np.zeros(I + 1, dtype=np.uint64), "clean_err": np.zeros(1, dtype=np.uint64)}
         rs.err, rs.clean_err = _ptr(out["err"], C.c_uint64), _ptr(out["clean_err"], C.c_uint64)
@@ -160,7 +170,8 @@ class LinkEngine:
                   "pa_p0": ((n_frames,), np.float32, C.c_float),
                   "alpha": ((n_frames, K), np.float32, C.c_float),
                   "rx_pos": ((n_frames, 3), np.float64, C.c_double),
-                  "clean_det": ((n_frames, N_SC), np.uint8, C.c_uint8)}
+                  "clean_det": ((n_frames, N_SC), np.uint8, C.c_uint8),
+                  "clean_err_per_frame": ((n_frames,), np.uint32, C.c_uint32)}
         for name in dumps:
             shape, dt, ct = shapes[name]
             out[name] = np.zeros(shape, dtype=dt)
@@ -172,10 +183,10 @@ class LinkEngine:
         return out
 
     def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
-                inject=None):
+                inject=None, noise_unit=False):
         """Asynchronous: H2D of injected inputs + kernels, counters accumulate on the device until fetch().
         Injected host arrays are kept alive until the next fetch()/synchronize()."""
-        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject)
+        rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject, noise_unit)
         self._keep.append(keep)
         _lib.check(self._lib, self._lib.mmimo_link_enqueue(self._h, C.byref(rq)))
 

@@ -1,0 +1,95 @@
+"""GPU: the drop-in `mp_model.Link` driven exactly like main_mp_miso_mcnc_ber_vs_ebn0.py:101-134 drives the
+reference's (one worker, same seeds) must reproduce the reference's shared error / bit counters stored in
+tests/golden/link_*.npz - through the fused frame kernel in "numpy" RNG mode (the reference's PCG64 streams are
+injected), through the building-block path (MMIMO_LINK_PATH=blocks), and statistically in "philox" mode."""
+import ctypes
+import multiprocessing as mp
+import os
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from test_gpu_dropin_blocks import M, build_objects, make_channel  # noqa: F401
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k8_los_csi", "link_k8_los_rapp"]
+
+
+def run_link(M, g, rng_mode="numpy", n_frames=None, bits_max=None, n_err_min=int(1e12), path="fused"):
+    n_fft, n_sc = int(g["n_fft"]), int(g["n_sc"])
+    mod, dist, tx, rx, arr = build_objects(M, int(g["n_ant"]), int(g["constel"]), n_fft, n_sc, 128 if n_fft >= 1024 else 16,
+                                           pa=str(g["pa"]), ibo=0.0)
+    ch = make_channel(M, str(g["chan"]), arr, rx)
+    nz = M["noise"].Awgn(snr_db=10, seed=1234)
+    nb = mod.n_bits_per_ofdm_sym
+    n_frames = int(g["n_frames"]) if n_frames is None else n_frames
+    csi = float(g["csi_eps"])
+    link = M["mp_model"].Link(mod_obj=mod, array_obj=arr, std_rx_obj=rx, chan_obj=ch, noise_obj=nz, rx_loc_var=10.0,
+                              n_err_min=n_err_min, bits_sent_max=nb * n_frames if bits_max is None else bits_max,
+                              is_mcnc=bool(g["is_mcnc"]), csi_epsylon=None if csi < 0 else csi)
+    link.rng_mode = rng_mode
+    link.update_distortion(ibo_val_db=float(g["ibo_db"]))
+    link.set_snr(snr_db_val=float(g["snr_db"]))
+    iters = np.asarray(g["iters"])
+    n_res = len(iters) + int(g["incl_clean"])
+    e = mp.Array(ctypes.c_double, n_res, lock=True)
+    b = mp.Array(ctypes.c_double, n_res, lock=True)
+    old = os.environ.get("MMIMO_LINK_PATH")
+    os.environ["MMIMO_LINK_PATH"] = path
+    try:
+        link.simulate(bool(g["incl_clean"]), True, iters, [int(s) for s in g["seeds"]], e, b)
+    finally:
+        if old is None:
+            del os.environ["MMIMO_LINK_PATH"]
+        else:
+            os.environ["MMIMO_LINK_PATH"] = old
+    return np.array(list(e)), np.array(list(b)), link
+
+
+def close_counts(got, want, slack):
+    """Error counters: equal, or off by a handful of bits where an fp32 slicer input fell on the other side of a
+    boundary than the reference's float64 one (a flipped symbol costs 1-2 bits and may persist over iterations)."""
+    return np.all(np.abs(np.asarray(got) - np.asarray(want)) <= slack)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_link_fused_numpy_streams_match_reference(M, name):
+    g = load_golden(name)
+    err, bits, link = run_link(M, g)
+    assert link._fused_ok()
+    assert np.array_equal(bits, g["bits"])
+    assert close_counts(err, g["err"], slack=12), (err, g["err"])
+
+
+@pytest.mark.parametrize("name", ["link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k16_los_small"])
+def test_link_block_path_matches_reference(M, name):
+    """The same loop composed from the drop-in building blocks (also the only path for n_fft != 4096)."""
+    g = load_golden(name)
+    err, bits, link = run_link(M, g, path="blocks")
+    assert np.array_equal(bits, g["bits"])
+    assert close_counts(err, g["err"], slack=12), (err, g["err"])
+
+
+def test_link_stop_rule_and_stream_rewind(M):
+    """bits_sent_max reached inside a batch: the counters stop exactly there and the generators are left where the
+    reference leaves them (here: a second simulate with the same seeds must give identical numbers)."""
+    g = load_golden("link_k8_los_rapp")
+    nb = 6 * 2048
+    err1, bits1, link = run_link(M, g, n_frames=5)
+    assert np.all(bits1 == 5 * nb)
+    # error threshold: slot 0 (most errors) stops first, the others keep counting
+    thr = int(err1[0] * 0.55)
+    err2, bits2, _ = run_link(M, g, n_frames=5, n_err_min=thr)
+    assert bits2[0] < 5 * nb and err2[0] >= thr and err2[0] - thr < nb
+    assert np.all(bits2[1:] >= bits2[0])
+
+
+def test_link_philox_mode_statistics(M):
+    g = load_golden("link_k64_los_mcnc")
+    err, bits, link = run_link(M, g, rng_mode="philox", n_frames=64)
+    ber = err / bits
+    # reference curve at Eb/N0 = 15 dB, IBO 0 dB: 0.089, 0.053, 0.035, 0.022, 0.0119, 0.0054
+    ref = np.array([0.089, 0.053, 0.035, 0.022, 0.0119, 0.0054])
+    assert np.all(np.abs(ber - ref) < 0.15 * ref + 5e-4), ber
