@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""BER-vs-Eb/N0 (or vs IBO) sweep on the fused B200 link kernels - the job of
+main_mp_clipping_noise_cancellation/main_mp_miso_{cnc,mcnc}_ber_vs_{ebn0,ibo}.py: same stopping rule
+(n_err_min / bits_sent_max per result row), same CSV row layout (row 0 swept axis, row 1 no distortion, row 2
+standard receiver, rows 3.. iterations 1..I; utilities.save_to_csv).  One process per GPU under torchrun; frames are
+sharded by global frame index and the counters all-reduced (parallel.monte_carlo_point).
+
+  python tools/ber_sweep.py --ebn0 5:20:0.5 --n-iter 8 --out ber.csv
+  torchrun --nproc-per-node 8 tools/ber_sweep.py --sweep ibo --ibo -9:9:0.5 --ebn0 15 --out ber_vs_ibo.csv
+"""
+import argparse
+import csv
+import math
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def axis(spec):
+    p = [float(v) for v in spec.split(":")]
+    if len(p) == 1:
+        return np.array(p)
+    return np.arange(p[0], p[1] + p[2] / 2, p[2])
+
+
+def run_sweep(eng, a, rank=0, world=1, exchange=None):
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200.parallel import link_batch_runner, monte_carlo_point
+    ebn0s, ibos = axis(a.ebn0), axis(a.ibo)
+    pts = [(e, ibos[0]) for e in ebn0s] if a.sweep == "ebn0" else [(ebn0s[0], i) for i in ibos]
+    bits_frame = int(math.log2(a.constel)) * 2048
+    rows = np.zeros((a.n_iter + 2, len(pts)))
+    frames = 0
+    for c, (ebn0, ibo) in enumerate(pts):
+        eng.set_ibo(float(ibo))
+        snr = 10 * math.log10(10 ** (ebn0 / 10) * math.log2(a.constel))  # ebn0_to_snr with n_fft := n_sub_carr
+        runner = link_batch_runner(eng, a.n_iter, snr, seed=a.seed + 7919 * c, csi_eps=a.csi_eps, incl_clean_run=True)
+        err, bits, n = monte_carlo_point(runner, a.n_iter + 2, bits_frame, int(a.err_min), int(a.bits_max), a.frames_per_step,
+                                         rank, world, exchange)
+        rows[:, c] = err / bits
+        frames += n
+    ax = ebn0s if a.sweep == "ebn0" else ibos
+    return ax, rows, frames
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--sweep", choices=["ebn0", "ibo"], default="ebn0")
+    ap.add_argument("--ebn0", default="5:20:0.5")
+    ap.add_argument("--ibo", default="0")
+    ap.add_argument("--n-ant", type=int, default=64)
+    ap.add_argument("--constel", type=int, default=64)
+    ap.add_argument("--channel", default="los", choices=["los", "two_path", "rayleigh"])
+    ap.add_argument("--receiver", default="mcnc", choices=["cnc", "mcnc"])
+    ap.add_argument("--pa", default="softlim", choices=["softlim", "rapp"])
+    ap.add_argument("--n-iter", type=int, default=8)
+    ap.add_argument("--csi-eps", type=float, default=0.0)
+    ap.add_argument("--bits-max", type=float, default=1e7)
+    ap.add_argument("--err-min", type=float, default=1e6)
+    ap.add_argument("--frames-per-step", type=int, default=1024)
+    ap.add_argument("--seed", type=int, default=2137)
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200.parallel import CounterExchange
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    exchange = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        exchange = CounterExchange(world, "cuda")
+    eng = LinkEngine(local)
+    eng.configure(constel_size=a.constel, n_ant=a.n_ant, pa=a.pa, ibo_db=axis(a.ibo)[0], channel=a.channel, receiver=a.receiver)
+    t0 = time.time()
+    ax, rows, frames = run_sweep(eng, a, rank, world, exchange)
+    dt = time.time() - t0
+    if rank == 0:
+        data = [list(ax)] + [list(r) for r in rows]
+        if a.out:
+            with open(a.out, "w", newline="") as fh:
+                csv.writer(fh).writerows(data)
+        print("--- Computation time: %f ---  (%d frames, %.0f frames/s, %d GPU)" % (dt, frames, frames / dt, world))
+        for r in data:
+            print(" ".join("%.3e" % v for v in r))
+    eng.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
