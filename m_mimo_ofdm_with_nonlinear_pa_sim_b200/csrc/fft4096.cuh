@@ -178,13 +178,24 @@ __device__ __forceinline__ void load_tw1(Tw1& tw, const float2* __restrict__ tw4
     for (int k = 1; k < 16; ++k) tw.w[k - 1] = tw4096[(t * k) & (FFT_N - 1)];
 }
 
+// Synchronisation policy of the two shared-memory exchanges of a transform (a template hook: the microbenchmark
+// tools/microbench/fft_phase_bench.cu instantiates the transform without barriers / without data movement to
+// measure the FMA-pipe and LSU-pipe demands separately).  SyncCta: the CTA of 256 threads runs one transform.
+struct SyncCta {
+    static constexpr bool kExchange = true;
+    __device__ __forceinline__ void x_begin() const {}
+    __device__ __forceinline__ void x_sync() const { __syncthreads(); }
+    __device__ __forceinline__ void x_end() const {}
+};
+
 // One full transform.  bufA/bufB: two 4096-entry shared buffers; tw2: shared table
 // W256^(n0 k1) at [k1*16 + n0] (forward sign).  x in: element j <-> index t + 256 j.
 // x out: element k2 <-> bin t + 256 k2.  Exactly two __syncthreads; safe to call back to back
 // (A/B alternate, see DESIGN.md "exchange buffers").
-template <int S, bool PRUNE_IN, bool PRUNE_OUT>
+template <int S, bool PRUNE_IN, bool PRUNE_OUT, class SYNC = SyncCta>
 __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf2* __restrict__ bufB,
-                                        const float2* __restrict__ tw2, const Tw1& tw1, const int t) {
+                                        const float2* __restrict__ tw2, const Tw1& tw1, const int t,
+                                        const SYNC sy = SYNC()) {
     // pass 1
     if (PRUNE_IN) {
         if ((t >> 5) == 0) radix16<S, false, false>(x);  // warp 0 holds the stray bin 1024 in x[4] of thread 0
@@ -197,12 +208,18 @@ __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf
         const float2 w = tw1.w[k - 1];
         x[k] = (S > 0) ? pcmulc(x[k], w.x, w.y) : pcmul(x[k], w.x, w.y);
     }
+    sy.x_begin();
+    if (SYNC::kExchange) {
 #pragma unroll
-    for (int k = 0; k < 16; ++k) bufA[k * 256 + t] = x[k];
-    __syncthreads();
+        for (int k = 0; k < 16; ++k) bufA[k * 256 + t] = x[k];
+    }
+    sy.x_sync();
     const int hi = t >> 4, lo = t & 15;
+    if (SYNC::kExchange) {
 #pragma unroll
-    for (int n1 = 0; n1 < 16; ++n1) x[n1] = bufA[hi * 256 + n1 * 16 + lo];
+        for (int n1 = 0; n1 < 16; ++n1) x[n1] = bufA[hi * 256 + n1 * 16 + lo];
+    }
+    sy.x_end();
     // pass 2
     radix16<S, false, false>(x);
 #pragma unroll
@@ -210,17 +227,19 @@ __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf
         const float2 w = tw2[k * 16 + lo];
         x[k] = (S > 0) ? pcmulc(x[k], w.x, w.y) : pcmul(x[k], w.x, w.y);
     }
-    {
+    sy.x_begin();
+    if (SYNC::kExchange) {
         const int base = hi * 16 + (lo ^ hi);
 #pragma unroll
         for (int k = 0; k < 16; ++k) bufB[k * 256 + base] = x[k];
     }
-    __syncthreads();
-    {
+    sy.x_sync();
+    if (SYNC::kExchange) {
         const int base = hi * 256 + lo * 16;
 #pragma unroll
         for (int n0 = 0; n0 < 16; ++n0) x[n0] = bufB[base + (n0 ^ lo)];
     }
+    sy.x_end();
     // pass 3
     if (PRUNE_OUT) {
         if ((t >> 5) == 0) radix16<S, false, false>(x);  // thread 0 also needs k2 = 4 (bin 1024)

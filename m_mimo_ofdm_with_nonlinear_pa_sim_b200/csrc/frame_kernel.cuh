@@ -188,7 +188,6 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             float2 nz[8];
             if (first && !a.rx_eq_in) {
                 if (a.noise) {
-#pragma unroll
                     const float ns = a.noise_unit ? sc.noise_sigma : 1.0f;
 #pragma unroll
                     for (int jp = 0; jp < 8; ++jp) {

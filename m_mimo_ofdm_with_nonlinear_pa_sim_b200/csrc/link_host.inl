@@ -6,7 +6,10 @@ static double calc_alpha_host(double ibo_db) {  // modulation.py:178-189
 }
 
 template <int PA>
-static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int grid) {
+static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int n) {
+    int per_sm = 2;
+    if (const char* e = getenv("MMIMO_CTAS_PER_SM")) per_sm = std::max(1, atoi(e));  // measurement knob
+    const int grid = std::min(n, per_sm * c->n_sm);
     k_link_frame<PA><<<grid, FFT_THREADS, FRAME_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
 }
 
@@ -247,7 +250,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.corr_out = want_corr ? c->corr.as<float2>() : nullptr;
         fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
         fa.err_total = counters;
-        const int grid = std::min(n, 2 * c->n_sm);
+        const int grid = n;
         prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {
             case MMIMO_PA_NONE: launch_frame<PA_NONE>(fa, c, grid); break;

@@ -1,0 +1,133 @@
+// Microbenchmark of the two resources of the fused frame kernel's antenna chain (IFFT -> PA -> FFT on 16 points per
+// thread): the butterfly arithmetic (FMA pipe) and the shared-memory exchanges (LSU pipe), alone and together, with
+// 1 and 2 CTAs of 256 threads per SM.  Prints SM cycles per antenna chain per CTA.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o fft_phase_bench fft_phase_bench.cu
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <vector>
+
+#include "../../m_mimo_ofdm_with_nonlinear_pa_sim_b200/csrc/frame_kernel.cuh"
+using namespace mmimo;
+
+struct SyncNone {  // compute only: no data movement, no barriers
+    static constexpr bool kExchange = false;
+    __device__ __forceinline__ void x_begin() const {}
+    __device__ __forceinline__ void x_sync() const {}
+    __device__ __forceinline__ void x_end() const {}
+};
+
+struct SyncNoBar {  // data movement without any barrier (results are wrong; timing experiment only)
+    static constexpr bool kExchange = true;
+    __device__ __forceinline__ void x_begin() const {}
+    __device__ __forceinline__ void x_sync() const {}
+    __device__ __forceinline__ void x_end() const {}
+};
+
+// MODE 4: full chain without barriers
+// MODE 0: full chain; 1: compute only; 2: exchange only (same addressing, 4 exchanges); 3: exchange without barriers
+template <int MODE>
+__global__ void __launch_bounds__(256, 2) k(float2* out, const float2* tw4096, const float2* tw256, int iters) {
+    extern __shared__ float2 smem[];
+    pf2* bufA = reinterpret_cast<pf2*>(smem);
+    pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
+    float2* tw2 = smem + 8192;
+    const int t = threadIdx.x;
+    tw2[t] = tw256[t];
+    Tw1 tw1;
+    load_tw1(tw1, tw4096, t);
+    __syncthreads();
+    pf2 x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = pk((float)(t + j) * 1e-3f, (float)(t - j) * 1e-3f);
+    const int hi = t >> 4, lo = t & 15;
+    for (int it = 0; it < iters; ++it) {
+        if (MODE == 0) {
+            fft4096<+1, true, false>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
+            fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
+        } else if (MODE == 4) {
+            fft4096<+1, true, false, SyncNoBar>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
+            fft4096<-1, false, true, SyncNoBar>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
+        } else if (MODE == 1) {
+            fft4096<+1, true, false, SyncNone>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
+            fft4096<-1, false, true, SyncNone>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
+        } else {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+#pragma unroll
+                for (int k2 = 0; k2 < 16; ++k2) bufA[k2 * 256 + t] = x[k2];
+                if (MODE == 2) __syncthreads();
+#pragma unroll
+                for (int n1 = 0; n1 < 16; ++n1) x[n1] = bufA[hi * 256 + n1 * 16 + lo];
+                {
+                    const int base = hi * 16 + (lo ^ hi);
+#pragma unroll
+                    for (int k2 = 0; k2 < 16; ++k2) bufB[k2 * 256 + base] = x[k2];
+                }
+                if (MODE == 2) __syncthreads();
+                {
+                    const int base = hi * 256 + lo * 16;
+#pragma unroll
+                    for (int n0 = 0; n0 < 16; ++n0) x[n0] = bufB[base + (n0 ^ lo)];
+                }
+            }
+        }
+    }
+    float2 s = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { const float2 v = unpk(x[j]); s.x += v.x; s.y += v.y; }
+    if (s.x == 123.456f) out[0] = s;
+}
+
+template <int MODE>
+static void run(const char* name, float2* d, const float2* t4, const float2* t2, int nsm, int per_sm) {
+    const int iters = 2000, smem = (8192 + 256) * 8 + (per_sm == 1 ? 110 * 1024 : 0);  // extra smem forces 1 CTA/SM
+    cudaFuncSetAttribute(k<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        cudaEventRecord(e0);
+        k<MODE><<<nsm * per_sm, 256, smem>>>(d, t4, t2, iters);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (rep) best = fminf(best, ms);
+    }
+    int clk; cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
+    const double cyc = best * 1e-3 * clk * 1e3;
+    printf("%-34s %d CTA/SM  %8.3f ms  %8.0f cycles/chain/CTA  %8.0f SM-cycles/chain\n", name, per_sm, best, cyc / iters, cyc / iters / per_sm);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) printf("CUDA error: %s\n", cudaGetErrorString(e));
+}
+
+int main() {
+    cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
+    printf("%s, %d SMs, clockRate %d kHz\n", p.name, p.multiProcessorCount, p.clockRate);
+    std::vector<float2> t4(4096), t2(256);
+    for (int i = 0; i < 4096; ++i) t4[i] = make_float2((float)cos(-2 * M_PI * i / 4096), (float)sin(-2 * M_PI * i / 4096));
+    for (int k1 = 0; k1 < 16; ++k1) for (int n0 = 0; n0 < 16; ++n0) t2[k1 * 16 + n0] = make_float2((float)cos(-2 * M_PI * k1 * n0 / 256), (float)sin(-2 * M_PI * k1 * n0 / 256));
+    float2 *d, *d4, *d2;
+    cudaMalloc(&d, 64); cudaMalloc(&d4, 4096 * 8); cudaMalloc(&d2, 256 * 8);
+    cudaMemcpy(d4, t4.data(), 4096 * 8, cudaMemcpyHostToDevice); cudaMemcpy(d2, t2.data(), 256 * 8, cudaMemcpyHostToDevice);
+    const int nsm = p.multiProcessorCount;
+    for (int per_sm = 1; per_sm <= 2; ++per_sm) {
+        run<0>("full chain (IFFT, PA, FFT)", d, d4, d2, nsm, per_sm);
+        run<1>("butterflies only (no exchange)", d, d4, d2, nsm, per_sm);
+        run<2>("4 exchanges only (STS, bar, LDS)", d, d4, d2, nsm, per_sm);
+        run<3>("4 exchanges, no barrier", d, d4, d2, nsm, per_sm);
+        run<4>("full chain, no barrier", d, d4, d2, nsm, per_sm);
+    }
+    return 0;
+}

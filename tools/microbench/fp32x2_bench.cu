@@ -10,7 +10,11 @@ __device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm volatile("mul.f32
 template <int MODE>
 __global__ void __launch_bounds__(256) k(float* out, int iters, float a, float b) {
     constexpr int N = 16;
-    float x[N]; u64 y[N];
+    float x[N]; u64 y[N]; unsigned z[N];
+    __shared__ unsigned sm[1024];
+    for (int i = threadIdx.x; i < 1024; i += 256) sm[i] = i;
+    __syncthreads();
+    for (int i = 0; i < N; ++i) z[i] = threadIdx.x * 7 + i;
     for (int i = 0; i < N; ++i) { x[i] = threadIdx.x + i; float2 t = make_float2(x[i], x[i] + 1); y[i] = *reinterpret_cast<u64*>(&t); }
     float2 ab = make_float2(a, b); u64 ab2 = *reinterpret_cast<u64*>(&ab);
     for (int it = 0; it < iters; ++it) {
@@ -25,10 +29,15 @@ __global__ void __launch_bounds__(256) k(float* out, int iters, float a, float b
                 if (MODE == 4) y[i] = mul2(y[i], ab2);
                 if (MODE == 5) { if (i & 1) y[i] = add2(y[i], ab2); else x[i] = fmaf(x[i], a, b); }   // mix FADD2 + FFMA
                 if (MODE == 6) { if (i & 1) y[i] = fma2(y[i], ab2, ab2); else x[i] = x[i] + a; }       // mix FFMA2 + FADD
+                if (MODE == 7) { if (i & 1) y[i] = fma2(y[i], ab2, ab2); else z[i] = (z[i] ^ (unsigned)it) + 0x9e3779b9u; }  // FFMA2 + (LOP3, IADD)
+                if (MODE == 8) { if (i & 1) y[i] = fma2(y[i], ab2, ab2); else z[i] ^= sm[(threadIdx.x + z[i]) & 255]; }    // FFMA2 + LDS (+LOP3s)
+                if (MODE == 9) { y[i] = fma2(y[i], ab2, ab2); sm[(threadIdx.x + 32 * i) & 1023] = (unsigned)it; }           // FFMA2 + STS 1:1
+                if (MODE == 10) { sm[(threadIdx.x + 32 * i) & 1023] = (unsigned)it; }                                        // STS only
             }
         }
     }
-    float s = 0; for (int i = 0; i < N; ++i) { float2 t = *reinterpret_cast<float2*>(&y[i]); s += x[i] + t.x + t.y; }
+    float s = 0; for (int i = 0; i < N; ++i) { float2 t = *reinterpret_cast<float2*>(&y[i]); s += x[i] + t.x + t.y + (float)z[i]; }
+    s += (float)sm[threadIdx.x];
     if (s == 123.456f) out[0] = s;
 }
 template <int MODE> void run(const char* name, float* d, int nsm, double lanes_per_inst) {
@@ -55,5 +64,9 @@ int main() {
     run<4>("FMUL2", d, p.multiProcessorCount, 2);
     run<5>("FADD2+FFMA 1:1", d, p.multiProcessorCount, 1.5);
     run<6>("FFMA2+FADD 1:1", d, p.multiProcessorCount, 1.5);
+    run<7>("FFMA2 + (LOP3+IADD) 8:8x2", d, p.multiProcessorCount, 1);
+    run<8>("FFMA2 + LDS chain 8:8", d, p.multiProcessorCount, 1);
+    run<9>("FFMA2 + STS 16:16", d, p.multiProcessorCount, 1);
+    run<10>("STS only 16", d, p.multiProcessorCount, 1);
     return 0;
 }
