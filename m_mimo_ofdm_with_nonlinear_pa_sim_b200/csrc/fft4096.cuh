@@ -171,7 +171,29 @@ __device__ __forceinline__ void radix16(pf2 (&x)[16]) {
 // transform uses the conjugates.  Kept in registers for the whole frame.
 struct Tw1 {
     float2 w[15];
+    __device__ __forceinline__ float2 at(int k) const { return w[k - 1]; }
 };
+
+// Compact variant: only W^t, W^2t, W^4t, W^8t live in registers (8 instead of 30); the other eleven twiddles are
+// products formed on the fly (11 complex multiplies per use).  Trades FMA work for registers / occupancy.
+struct Tw1Compact {
+    float2 w1, w2, w4, w8;
+    __device__ __forceinline__ float2 at(int k) const {
+        float2 r = make_float2(1.f, 0.f);
+        bool first = true;
+        if (k & 1) { r = w1; first = false; }
+        if (k & 2) { r = first ? w2 : cmul(r, w2); first = false; }
+        if (k & 4) { r = first ? w4 : cmul(r, w4); first = false; }
+        if (k & 8) { r = first ? w8 : cmul(r, w8); first = false; }
+        return r;
+    }
+};
+__device__ __forceinline__ void load_tw1(Tw1Compact& tw, const float2* __restrict__ tw4096, int t) {
+    tw.w1 = tw4096[t & (4096 - 1)];
+    tw.w2 = tw4096[(2 * t) & (4096 - 1)];
+    tw.w4 = tw4096[(4 * t) & (4096 - 1)];
+    tw.w8 = tw4096[(8 * t) & (4096 - 1)];
+}
 
 __device__ __forceinline__ void load_tw1(Tw1& tw, const float2* __restrict__ tw4096, int t) {
 #pragma unroll
@@ -192,10 +214,16 @@ struct SyncCta {
 // W256^(n0 k1) at [k1*16 + n0] (forward sign).  x in: element j <-> index t + 256 j.
 // x out: element k2 <-> bin t + 256 k2.  Exactly two __syncthreads; safe to call back to back
 // (A/B alternate, see DESIGN.md "exchange buffers").
-template <int S, bool PRUNE_IN, bool PRUNE_OUT, class SYNC = SyncCta>
+struct NoHook {
+    __device__ __forceinline__ void operator()() const {}
+};
+
+// `before_pass3` runs after the loads of the second exchange have been issued and before the last radix-16 pass:
+// the frame kernel issues the next antenna's global loads there, so that their latency hides behind that pass.
+template <int S, bool PRUNE_IN, bool PRUNE_OUT, class SYNC = SyncCta, class HOOK = NoHook, class TW = Tw1>
 __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf2* __restrict__ bufB,
-                                        const float2* __restrict__ tw2, const Tw1& tw1, const int t,
-                                        const SYNC sy = SYNC()) {
+                                        const float2* __restrict__ tw2, const TW& tw1, const int t,
+                                        const SYNC sy = SYNC(), const HOOK before_pass3 = HOOK()) {
     // pass 1
     if (PRUNE_IN) {
         if ((t >> 5) == 0) radix16<S, false, false>(x);  // warp 0 holds the stray bin 1024 in x[4] of thread 0
@@ -205,7 +233,7 @@ __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf
     }
 #pragma unroll
     for (int k = 1; k < 16; ++k) {
-        const float2 w = tw1.w[k - 1];
+        const float2 w = tw1.at(k);
         x[k] = (S > 0) ? pcmulc(x[k], w.x, w.y) : pcmul(x[k], w.x, w.y);
     }
     sy.x_begin();
@@ -240,6 +268,7 @@ __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf
         for (int n0 = 0; n0 < 16; ++n0) x[n0] = bufB[base + (n0 ^ lo)];
     }
     sy.x_end();
+    before_pass3();
     // pass 3
     if (PRUNE_OUT) {
         if ((t >> 5) == 0) radix16<S, false, false>(x);  // thread 0 also needs k2 = 4 (bin 1024)

@@ -51,9 +51,10 @@ struct FrameArgs {
     float2* corr_out;            // [F][I+1][2048] corrected symbols fed to the slicer, or nullptr
     uint32_t* err_out;           // [F][I+1], or nullptr
     unsigned long long* err_total;  // [I+1] accumulated with atomics
+    float2* rxeq_scratch;        // [gridDim.x][2048] per-CTA scratch for the equalised received signal (stays in L2)
 };
 
-constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048 + 2048;
+constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048;
 constexpr int FRAME_SMEM_BYTES = FRAME_SMEM_FLOAT2 * 8 + 64 * 4;
 
 // packed PA (distortion.py:9-19 soft limiter, :102-113 Rapp, :202-211 third order)
@@ -75,16 +76,18 @@ __device__ __forceinline__ pf2 pa_apply_pk(pf2 xp, const float p0, const float s
 }
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 // One antenna: x (8 data slots, already precoded, 1/64 folded in) -> IFFT -> PA -> FFT; on return
 // x[0..3], x[12..15] hold the data bins of this thread (thread 0: x[4] = bin 1024).
-template <int PA>
+template <int PA, class HOOK = NoHook>
 __device__ __forceinline__ void antenna_chain(pf2 (&x)[16], pf2* bufA, pf2* bufB, const float2* tw2, const Tw1& tw1,
-                                              const int t, const float p0, const float sqrt_p0, const float p1) {
+                                              const int t, const float p0, const float sqrt_p0, const float p1,
+                                              const HOOK before_last_pass = HOOK()) {
     fft4096<+1, true, false>(x, bufA, bufB, tw2, tw1, t);
 #pragma unroll
     for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA>(x[j], p0, sqrt_p0, p1);
-    fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t);
+    fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t, SyncCta(), before_last_pass);
 }
 
 template <int PA>
@@ -95,8 +98,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
     pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
     float2* tw2 = smem + 8192;
     float2* symn_s = tw2 + 256;      // scaled current symbols, thread-private addresses jp*256+t
-    float2* rxeq_s = symn_s + 2048;  // equalised received signal, thread-private addresses
-    unsigned int* err_s = reinterpret_cast<unsigned int*>(rxeq_s + 2048);
+    // equalised received signal: written once per frame, read once per pass, thread-private addresses -> global
+    // scratch (L2-resident) instead of 16 KB of shared memory, which leaves the L1 room for the channel rows
+    float2* rxeq_s = a.rxeq_scratch + (size_t)blockIdx.x * N_SC;
+    unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + 2048);
 
     const int t = threadIdx.x;
     tw2[t] = tw256[t];
@@ -149,6 +154,11 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
 #pragma unroll
             for (int jp = 0; jp < 8; ++jp) acc[jp] = pk(0.f, 0.f);
 
+            pf2 rown[8];  // precoder / channel-knowledge row of the NEXT antenna, loaded one transform pass ahead
+            if (K > 0) {
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) rown[jp] = pk2(__ldg(Hp + jp * 256 + t));
+            }
             for (int k = 0; k < K; ++k) {
                 const float2* __restrict__ pr = Hp + (size_t)k * N_SC;
                 const float2* __restrict__ hk = Hm + (size_t)k * N_SC;
@@ -163,20 +173,24 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
 #pragma unroll
                     for (int jp = 0; jp < 8; ++jp) {
                         const float2 s = symn_s[jp * 256 + t];
-                        x[jp_to_j(jp)] = pcmul(pk2(__ldg(pr + jp * 256 + t)), s.x, s.y);
+                        x[jp_to_j(jp)] = pcmul(rown[jp], s.x, s.y);
                     }
                 } else {
 #pragma unroll
                     for (int jp = 0; jp < 8; ++jp) {  // conj(h) * (c + j s) = (h.x c + h.y s, h.x s - h.y c)
                         const float2 s = symn_s[jp * 256 + t];
-                        const pf2 h = pk2(__ldg(pr + jp * 256 + t));
+                        const pf2 h = rown[jp];
                         x[jp_to_j(jp)] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));
                     }
                 }
 #pragma unroll
                 for (int j = 4; j < 12; ++j) x[j] = pk(0.f, 0.f);
                 if (t == 0) { x[4] = x[0]; x[0] = pk(0.f, 0.f); }
-                antenna_chain<PA>(x, bufA, bufB, tw2, tw1, t, p0, sqrt_p0, a.pa_p1);
+                const float2* __restrict__ prn = pr + (k + 1 < K ? N_SC : 0);
+                antenna_chain<PA>(x, bufA, bufB, tw2, tw1, t, p0, sqrt_p0, a.pa_p1, [&]() {
+#pragma unroll
+                    for (int jp = 0; jp < 8; ++jp) rown[jp] = pk2(__ldg(prn + jp * 256 + t));
+                });
                 if (t == 0) x[0] = x[4];
 #pragma unroll
                 for (int jp = 0; jp < 8; ++jp) acc[jp] = pcfma(x[jp_to_j(jp)], pk2(__ldg(hk + jp * 256 + t)), acc[jp]);

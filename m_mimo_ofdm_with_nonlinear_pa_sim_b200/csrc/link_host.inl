@@ -8,7 +8,7 @@ static double calc_alpha_host(double ibo_db) {  // modulation.py:178-189
 template <int PA>
 static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int n) {
     int per_sm = 2;
-    if (const char* e = getenv("MMIMO_CTAS_PER_SM")) per_sm = std::max(1, atoi(e));  // measurement knob
+    if (const char* e = getenv("MMIMO_CTAS_PER_SM")) per_sm = std::min(8, std::max(1, atoi(e)));  // measurement knob
     const int grid = std::min(n, per_sm * c->n_sm);
     k_link_frame<PA><<<grid, FFT_THREADS, FRAME_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
 }
@@ -250,6 +250,8 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.corr_out = want_corr ? c->corr.as<float2>() : nullptr;
         fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
         fa.err_total = counters;
+        if (c->rxeq_scr.reserve((size_t)8 * c->n_sm * N_SC * 8)) return 1;  // >= the largest grid launch_frame uses
+        fa.rxeq_scratch = c->rxeq_scr.as<float2>();
         const int grid = n;
         prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {

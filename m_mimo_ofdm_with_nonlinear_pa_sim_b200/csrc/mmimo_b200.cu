@@ -65,7 +65,7 @@ struct mmimo_ctx {
     // tables
     DevBuf tw4096, tw256, freq_slot, freq_bin, tx_pos;
     // per-chunk scratch
-    DevBuf h_true, h_loop, csi_nz, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
+    DevBuf h_true, h_loop, csi_nz, rxeq_scr, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // stage-op scratch
@@ -182,7 +182,7 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->v, &c->sscale, &c->agc_inv,
+    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->rxeq_scr, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
                      &c->s_a, &c->s_b, &c->s_c, &c->s_d};

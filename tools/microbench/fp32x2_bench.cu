@@ -12,6 +12,7 @@ __global__ void __launch_bounds__(256) k(float* out, int iters, float a, float b
     constexpr int N = 16;
     float x[N]; u64 y[N]; unsigned z[N];
     __shared__ unsigned sm[1024];
+    u64* sm64 = reinterpret_cast<u64*>(sm);
     for (int i = threadIdx.x; i < 1024; i += 256) sm[i] = i;
     __syncthreads();
     for (int i = 0; i < N; ++i) z[i] = threadIdx.x * 7 + i;
@@ -32,6 +33,10 @@ __global__ void __launch_bounds__(256) k(float* out, int iters, float a, float b
                 if (MODE == 7) { if (i & 1) y[i] = fma2(y[i], ab2, ab2); else z[i] = (z[i] ^ (unsigned)it) + 0x9e3779b9u; }  // FFMA2 + (LOP3, IADD)
                 if (MODE == 8) { if (i & 1) y[i] = fma2(y[i], ab2, ab2); else z[i] ^= sm[(threadIdx.x + z[i]) & 255]; }    // FFMA2 + LDS (+LOP3s)
                 if (MODE == 9) { y[i] = fma2(y[i], ab2, ab2); sm[(threadIdx.x + 32 * i) & 1023] = (unsigned)it; }           // FFMA2 + STS 1:1
+                if (MODE == 11) { y[i] = fma2(y[i], ab2, ab2); y[(i + 1) & 15] = fma2(y[(i + 1) & 15], ab2, ab2); sm[(threadIdx.x + 32 * i) & 1023] = (unsigned)it; }  // 2 FFMA2 : 1 STS.32
+                if (MODE == 12) { y[i] = fma2(y[i], ab2, ab2); y[(i + 1) & 15] = fma2(y[(i + 1) & 15], ab2, ab2); y[(i + 2) & 15] = fma2(y[(i + 2) & 15], ab2, ab2); y[(i + 3) & 15] = fma2(y[(i + 3) & 15], ab2, ab2); sm64[(threadIdx.x + 32 * i) & 511] = y[i]; }  // 4 FFMA2 : 1 STS.64
+                if (MODE == 13) { y[i] = fma2(y[i], ab2, ab2); y[(i + 1) & 15] = fma2(y[(i + 1) & 15], ab2, ab2); y[(i + 2) & 15] = fma2(y[(i + 2) & 15], ab2, ab2); y[(i + 3) & 15] = fma2(y[(i + 3) & 15], ab2, ab2); }  // 4 FFMA2 only
+                if (MODE == 14) { sm64[(threadIdx.x + 32 * i) & 511] = y[i]; y[i] += 1; }  // STS.64 only
                 if (MODE == 10) { sm[(threadIdx.x + 32 * i) & 1023] = (unsigned)it; }                                        // STS only
             }
         }
@@ -68,5 +73,9 @@ int main() {
     run<8>("FFMA2 + LDS chain 8:8", d, p.multiProcessorCount, 1);
     run<9>("FFMA2 + STS 16:16", d, p.multiProcessorCount, 1);
     run<10>("STS only 16", d, p.multiProcessorCount, 1);
+    run<11>("2 FFMA2 : 1 STS.32 (balanced)", d, p.multiProcessorCount, 1);
+    run<12>("4 FFMA2 : 1 STS.64 (balanced)", d, p.multiProcessorCount, 1);
+    run<13>("4 FFMA2 only", d, p.multiProcessorCount, 1);
+    run<14>("STS.64 only", d, p.multiProcessorCount, 1);
     return 0;
 }
