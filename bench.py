@@ -288,6 +288,14 @@ def run_gpu(a):
         # algorithmic HBM bytes of the fused kernel per frame: the K channel rows re-read by every pass (the MRT
         # precoder is derived from them on the fly) + AGC / symbol-scale vectors
         bytes_frame = (I + 1) * a.n_ant * N_SC * 8 + (I + 1) * N_SC * 12
+        # measured DRAM traffic of the kernel from the committed ncu capture, scaled to this launch size (same K, I only)
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "frame_kernel_traffic.json")))
+            if tr["n_ant"] == a.n_ant and tr["n_iter"] == I:
+                traffic = tr["dram_bytes_per_frame"] * F
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -299,7 +307,9 @@ def run_gpu(a):
                             "D2H of the 65 counters inside every timed step"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                         "traffic_note": "dram__bytes_read+write per launch from profiles/frame_kernel_traffic.json (ncu --set full, "
+                                         "1184-frame launch) scaled to this launch's frame count; algorithmic HBM bytes per launch = %d" % (bytes_frame * F),
                          "kernel": "k_link_frame<soft limiter>", "launches_timed": frame_n,
                          "kernel_ms_per_launch": frame_ms / max(frame_n, 1),
                          "kernel_share_of_step": frame_ms / ms_total if ms_total else None,
