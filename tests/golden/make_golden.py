@@ -323,6 +323,7 @@ def golden_small():
 
 
 if __name__ == "__main__":
+    golden_full_size_extras()
     golden_small()
     golden_stages()
     golden_link("link_k64_los_mcnc", 64, "los", 0.0, 15.0, 3, [0, 1, 2, 3, 4, 5], [1, 2, 3])
@@ -333,3 +334,78 @@ if __name__ == "__main__":
     golden_link("link_k8_los_rapp", 8, "los", 1.0, 15.0, 2, [0, 1, 2], [41, 42, 43], pa="rapp")
     golden_link("link_k16_los_small", 16, "los", 0.0, 15.0, 4, [0, 1, 2, 3, 4, 5, 6, 7, 8], [51, 52, 53],
                 n_fft=1024, n_sc=512, constel=16)
+
+
+def golden_full_size_extras():
+    """Full-size (n_fft 4096 / 2048 sub-carriers) cases for BASELINE configs 4 and 5: SDR snapshots as
+    main_beampatterns_plotting/sdr_mp.py:124-151 computes them, and the two-user MRT / ZF frame of
+    main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642 (per-user McncMuReceiver that knows the other user's bits)."""
+    out = {}
+    n_ant = 8
+    # ---- SDR (config 4) ----
+    my_mod, my_dist, my_tx, my_rx, my_array = build_objects(n_ant)
+    rng = np.random.default_rng(17)
+    des, dis, poss, bits_l = [], [], [], []
+    for ibo in (0.0, 3.0):
+        my_rx.set_position(212.0 + rng.uniform(-5, 5), 212.0 + rng.uniform(-5, 5), 1.5)
+        ch = make_channel("los", my_array, my_rx)
+        my_array.set_precoding_matrix(channel_mat_fd=ch.channel_mat_fd, mr_precoding=True)
+        my_array.update_distortion(ibo_db=ibo, avg_sample_pow=my_mod.avg_sample_power)
+        vk = my_array.get_precoding_mat()
+        vk_pow = np.sum(np.power(np.abs(vk), 2), axis=1)
+        ibo_vec = 10 * np.log10(10 ** (ibo / 10) * my_mod.n_sub_carr / (vk_pow * n_ant))
+        ak = np.expand_dims(my_mod.calc_alpha(ibo_db=ibo_vec), axis=1)
+        bits = rng.choice((0, 1), my_mod.n_bits_per_ofdm_sym)
+        x_fd, x_clean = my_array.transmit(bits, out_domain_fd=True, skip_dist=False, return_both=True)
+        rx = ch.propagate(in_sig_mat=x_fd, sum_signals=False)
+        rx_sc = np.concatenate((rx[:, -1024:], rx[:, 1:1025]), axis=1)
+        cl = ch.propagate(in_sig_mat=x_clean, sum_signals=False)
+        cl_sc = np.concatenate((cl[:, -1024:], cl[:, 1:1025]), axis=1)
+        dist_sig = rx_sc - ak * cl_sc
+        des.append(np.sum(np.abs(np.sum(ak * cl_sc, axis=0)) ** 2))
+        dis.append(np.sum(np.abs(np.sum(dist_sig, axis=0)) ** 2))
+        poss.append((my_rx.cord_x, my_rx.cord_y, my_rx.cord_z))
+        bits_l.append(bits.astype(np.uint8))
+    out["sdr_ibo"] = np.array([0.0, 3.0])
+    out["sdr_pos"] = np.array(poss)
+    out["sdr_bits"] = np.stack(bits_l)
+    out["sdr_desired"] = np.array(des)
+    out["sdr_distortion"] = np.array(dis)
+
+    # ---- two users (config 5) ----
+    mod2, dist2, tx2, rx2, arr2 = build_objects(n_ant, n_users=2)
+    rxs = [copy.deepcopy(rx2), copy.deepcopy(rx2)]
+    rxs[0].set_position(np.cos(np.deg2rad(-30)) * 100.0, np.sin(np.deg2rad(-30)) * 100.0, 1.5)
+    rxs[1].set_position(np.cos(np.deg2rad(30)) * 316.3, np.sin(np.deg2rad(30)) * 316.3, 1.5)
+    chans = [make_channel("los", arr2, r) for r in rxs]
+    hl = [c.get_channel_mat_fd() for c in chans]
+    out["mu_h"] = np.stack(hl)
+    bits_mu = rng.choice((0, 1), (2, mod2.n_bits_per_ofdm_sym))
+    out["mu_bits"] = bits_mu.astype(np.uint8)
+    for tag, kw in (("mrt", dict(mr_precoding=True)), ("zf", dict(zf_precoding=True))):
+        rcv = []
+        for u in range(2):
+            arr_u = copy.deepcopy(arr2)
+            rcv.append(corrector.McncMuReceiver(arr_u, copy.deepcopy(chans[u]), usr_idx=u))
+        arr2.set_precoding_matrix(channel_mat_fd=hl, **kw)
+        arr2.update_distortion(ibo_db=2.0, avg_sample_pow=mod2.avg_sample_power)
+        out["mu_v_" + tag] = arr2.get_precoding_mat()
+        out["mu_sat_pow_" + tag] = arr2.array_elements[0].impairment.sat_pow
+        x = arr2.transmit(bits_mu, out_domain_fd=True)
+        out["mu_x_fd_rows07_" + tag] = x[[0, 7]]
+        for u in range(2):
+            rcv[u].antenna_array.set_precoding_matrix(channel_mat_fd=hl, **kw)
+            rcv[u].antenna_array.update_distortion(ibo_db=2.0, avg_sample_pow=mod2.avg_sample_power)
+            rcv[u].update_agc()
+            y = chans[u].propagate(in_sig_mat=x)
+            nz = noise.Awgn(snr_db=28.0, seed=40 + u)
+            y = nz.process(y, avg_sample_pow=float(np.mean(np.abs(y[np.r_[1:1025, 3072:4096]]) ** 2)))
+            y = y / rcv[u].agc_corr_vec
+            res = rcv[u].receive(n_iters_lst=[0, 1, 2], in_sig_fd=y, other_usr_bits=bits_mu[1 - u])
+            out["mu_rx_eq_%s_u%d" % (tag, u)] = y
+            out["mu_agc_%s_u%d" % (tag, u)] = rcv[u].agc_corr_vec
+            out["mu_det_%s_u%d" % (tag, u)] = np.stack([bits2idx(b, 6) for b in res])
+            out["mu_err_%s_u%d" % (tag, u)] = np.array([int(np.sum(b != bits_mu[u])) for b in res])
+    np.savez_compressed(os.path.join(HERE, "full_size_extras.npz"), **out)
+    print("full_size_extras ok: sdr", out["sdr_desired"] / out["sdr_distortion"],
+          "mu err", {k: v.tolist() for k, v in out.items() if k.startswith("mu_err")})
