@@ -93,3 +93,39 @@ def test_link_philox_mode_statistics(M):
     # reference curve at Eb/N0 = 15 dB, IBO 0 dB: 0.089, 0.053, 0.035, 0.022, 0.0119, 0.0054
     ref = np.array([0.089, 0.053, 0.035, 0.022, 0.0119, 0.0054])
     assert np.all(np.abs(ber - ref) < 0.15 * ref + 5e-4), ber
+
+
+def _runner_pattern(M, n_workers, rng_mode):
+    """The launcher of main_mp_miso_mcnc_ber_vs_ebn0.py:121-141: shared counters, one mp.Process per worker running
+    link.simulate with its own seeds, join, BER = errors / bits."""
+    g = load_golden("link_k8_los_rapp")
+    mod, dist, tx, rx, arr = build_objects(M, 8, pa="softlim", ibo=0.0)
+    ch = make_channel(M, "los", arr, rx)
+    link = M["mp_model"].Link(mod_obj=mod, array_obj=arr, std_rx_obj=rx, chan_obj=ch, noise_obj=M["noise"].Awgn(snr_db=10, seed=1234),
+                              rx_loc_var=10.0, n_err_min=int(1e9), bits_sent_max=12288 * 40, is_mcnc=True)
+    link.rng_mode = rng_mode
+    link.update_distortion(ibo_val_db=0.0)
+    link.set_snr(snr_db_val=float(M["utilities"].ebn0_to_snr(15.0, 2048, 2048, 64)))
+    iters = np.array([0, 1, 2, 3])
+    e = mp.Array(ctypes.c_double, len(iters) + 1, lock=True)
+    b = mp.Array(ctypes.c_double, len(iters) + 1, lock=True)
+    seeds = np.random.default_rng(2137).integers(0, 2 ** 62, size=(n_workers, 3))
+    procs = [mp.Process(target=link.simulate, args=(True, True, iters, seeds[i], e, b)) for i in range(n_workers)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    return np.array(list(e)), np.array(list(b))
+
+
+@pytest.mark.parametrize("rng_mode", ["numpy", "philox"])
+def test_multiprocessing_runner_pattern(M, rng_mode):
+    """Two worker PROCESSES (spawned: CUDA contexts do not survive fork) sharing the counters like the reference's runners."""
+    assert mp.get_start_method() == "spawn"  # set by importing the drop-in mp_model
+    err, bits = _runner_pattern(M, 2, rng_mode)
+    # every slot stops at bits_sent_max; two workers may overshoot by at most one frame each (like the reference)
+    assert np.all(bits >= 12288 * 40) and np.all(bits <= 12288 * 42)
+    ber = err / bits
+    assert ber[0] < 5e-3                                  # no distortion
+    assert 0.05 < ber[1] < 0.14 and np.all(np.diff(ber[1:]) < 0)  # standard RX, then improving with MCNC iterations
