@@ -135,6 +135,22 @@ int mmimo_link_fetch(mmimo_ctx* ctx, int32_t n_iter, uint64_t* err, uint64_t* cl
  * into caller-owned DEVICE memory - the buffer handed to the NCCL all-reduce that replaces the shared
  * multiprocessing.Array accumulation of mp_model.py:172-173,221-222; clear != 0 zeroes the counters after the copy */
 int mmimo_counters_to_device(mmimo_ctx* ctx, void* dst_dev, int clear);
+/* Signal-to-distortion snapshots (main_beampatterns_plotting/sdr_mp.py:124-151): for n_frames channel realisations of the
+ * configured link (receiver position re-drawn per snapshot like mp_model.py:193-198, MRT precoding, the configured PA/IBO)
+ * desired[i]    = sum_s | sum_k alpha_k h_k X_clean_k |^2   and
+ * distortion[i] = sum_s | sum_k h_k (X_k - alpha_k X_clean_k) |^2 , alpha_k the per-antenna Bussgang coefficient.
+ * Optional injected inputs as in mmimo_sim_request (NULL = generated on the device). */
+typedef struct mmimo_sdr_request {
+    int32_t n_frames;
+    int32_t reserved;
+    uint64_t seed;
+    uint64_t frame_id0;
+    const double* rx_pos;      /* [n_frames][3] */
+    const float* h_true;       /* c64 [n_frames][n_ant][n_sub_carr] */
+    const uint8_t* tx_idx;     /* [n_frames][n_sub_carr] */
+} mmimo_sdr_request;
+int mmimo_sdr_simulate(mmimo_ctx* ctx, const mmimo_sdr_request* req, double* desired, double* distortion);
+
 /* number of kernels launched by this context so far (bench.py "gpu_launches") */
 uint64_t mmimo_launch_count(mmimo_ctx* ctx);
 

@@ -33,6 +33,11 @@ class SimResult(C.Structure):
                 ("agc", c_f_p), ("pa_p0", c_f_p), ("alpha", c_f_p), ("rx_pos", c_d_p), ("clean_det", c_u8_p), ("clean_err_per_frame", c_u32_p)]
 
 
+class SdrRequest(C.Structure):
+    _fields_ = [("n_frames", C.c_int32), ("reserved", C.c_int32), ("seed", C.c_uint64), ("frame_id0", C.c_uint64),
+                ("rx_pos", c_d_p), ("h_true", c_f_p), ("tx_idx", c_u8_p)]
+
+
 class MmimoError(RuntimeError):
     pass
 
@@ -42,7 +47,7 @@ _LIB = None
 # every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
            "mmimo_set_stream", "mmimo_counters_to_device",
-           "mmimo_configure", "mmimo_set_ibo", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
+           "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
            "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
            "mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_array_transmit",
@@ -87,6 +92,7 @@ def load(build_if_missing: bool = True):
     lib.mmimo_link_simulate.argtypes = [C.c_void_p, C.POINTER(SimRequest), C.POINTER(SimResult)]
     lib.mmimo_link_enqueue.argtypes = [C.c_void_p, C.POINTER(SimRequest)]
     lib.mmimo_link_fetch.argtypes = [C.c_void_p, C.c_int32, c_u64_p, c_u64_p]
+    lib.mmimo_sdr_simulate.argtypes = [C.c_void_p, C.POINTER(SdrRequest), c_d_p, c_d_p]
     lib.mmimo_launch_count.argtypes = [C.c_void_p]
     lib.mmimo_launch_count.restype = C.c_uint64
     lib.mmimo_profile.argtypes = [C.c_void_p, C.c_int]

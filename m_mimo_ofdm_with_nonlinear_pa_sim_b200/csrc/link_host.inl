@@ -317,3 +317,71 @@ extern "C" int mmimo_link_simulate(mmimo_ctx* c, const mmimo_sim_request* rq, mm
     rs->bits_per_frame = (uint64_t)(2 * log2_side(c->cfg.constel_size)) * N_SC;
     return mmimo_link_fetch(c, rq->n_iter, rs->err, rs->clean_err);
 }
+
+template <int PA>
+static void launch_sdr(const SdrArgs& sa, const mmimo_ctx* c, int n) {
+    k_sdr_frame<PA><<<std::min(n, 2 * c->n_sm), FFT_THREADS, SDR_SMEM_BYTES, c->stream>>>(sa, c->tw4096.as<float2>(), c->tw256.as<float2>());
+}
+
+extern "C" int mmimo_sdr_simulate(mmimo_ctx* c, const mmimo_sdr_request* rq, double* desired, double* distortion) {
+    if (!c || !rq || !desired || !distortion) return fail("mmimo_sdr_simulate: NULL argument");
+    if (!c->configured) return fail("mmimo_sdr_simulate: context not configured (call mmimo_configure)");
+    if (rq->n_frames <= 0) return 0;
+    CK(cudaSetDevice(c->device));
+    const mmimo_link_config& cfg = c->cfg;
+    const int K = cfg.n_ant;
+    mmimo_sim_request lr{};
+    lr.n_frames = rq->n_frames; lr.snr_db = 100.0; lr.seed = rq->seed; lr.frame_id0 = rq->frame_id0;
+    const size_t chunk = std::min<size_t>({(size_t)rq->n_frames, (size_t)8192, std::max<size_t>(1, c->scratch_budget / ((size_t)K * N_SC * 8 + 65536))});
+    if (c->h_true.reserve(chunk * K * N_SC * 8) || c->sscale.reserve(chunk * N_SC * 4) || c->agc_inv.reserve(chunk * N_SC * 8) ||
+        c->hkvk_inv.reserve(chunk * N_SC * 8) || c->scal.reserve(chunk * sizeof(FrameScalars)) || c->alpha.reserve(chunk * K * 4) ||
+        c->rx_pos.reserve(chunk * 24) || c->tx_idx.reserve(chunk * N_SC) || c->s_b.reserve(chunk * 16))
+        return 1;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(k_sdr_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_sdr_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_sdr_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_sdr_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+        attr_set = true;
+    }
+    for (size_t c0 = 0; c0 < (size_t)rq->n_frames; c0 += chunk) {
+        const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
+        float2 *h_true = nullptr, *h_loop = nullptr;
+        RealisationIn in{rq->rx_pos, rq->h_true, nullptr, nullptr, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
+        if (run_realisation(c, &lr, in, c0, n, &h_true, &h_loop, false)) return 1;
+        SdrArgs sa{};
+        const long long hfs = (long long)K * N_SC;
+        sa.tx.h_mac = h_true; sa.tx.h_mac_fs = hfs;
+        sa.tx.h_pre = h_true; sa.tx.h_pre_fs = hfs;
+        sa.tx.v = nullptr; sa.tx.v_fs = 0;
+        sa.tx.sscale = c->sscale.as<float>(); sa.tx.sscale_fs = N_SC;
+        sa.tx.agc_inv = c->agc_inv.as<float2>(); sa.tx.agc_fs = N_SC;
+        sa.tx.k = K;
+        sa.scal = c->scal.as<FrameScalars>();
+        sa.alpha = c->alpha.as<float>();
+        sa.pa_p1 = (float)cfg.p_hardness;
+        sa.qam.log2side = log2_side(cfg.constel_size);
+        sa.n_frames = n;
+        sa.tx_idx = nullptr;
+        if (rq->tx_idx) {
+            if (upload_native<uint8_t>(c, rq->tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;
+            sa.tx_idx = c->tx_idx.as<uint8_t>();
+        }
+        sa.seed = rq->seed; sa.frame_id0 = rq->frame_id0 + c0;
+        sa.desired = c->s_b.as<double>();
+        sa.distortion = c->s_b.as<double>() + n;
+        switch (cfg.pa_kind) {
+            case MMIMO_PA_NONE: launch_sdr<PA_NONE>(sa, c, n); break;
+            case MMIMO_PA_SOFT_LIMITER: launch_sdr<PA_SOFT_LIMITER>(sa, c, n); break;
+            case MMIMO_PA_RAPP: launch_sdr<PA_RAPP>(sa, c, n); break;
+            default: launch_sdr<PA_TOI>(sa, c, n); break;
+        }
+        c->launches++;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(desired + c0, sa.desired, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(distortion + c0, sa.distortion, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}

@@ -1,7 +1,7 @@
 // Per-realisation kernels: channel generation, MRT precoder + AGC / alpha / noise bookkeeping,
 // and the FFT-free "no distortion" frame.  All per-sub-carrier arrays use the native slot order.
 #pragma once
-#include "frame_kernel.cuh"
+#include "sdr_kernel.cuh"
 
 namespace mmimo {
 

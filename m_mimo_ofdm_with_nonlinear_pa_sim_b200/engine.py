@@ -182,6 +182,31 @@ class LinkEngine:
         out["bits"] = int(rs.bits_per_frame) * int(n_frames)
         return out
 
+    def sdr(self, n_frames, *, seed=0, frame_id0=0, inject=None):
+        """Signal-to-distortion snapshots of the configured link (main_beampatterns_plotting/sdr_mp.py:124-151):
+        returns (desired[n_frames], distortion[n_frames]) powers; SDR per snapshot = desired / distortion.
+        inject: optional rx_pos [n,3], h_true [n,K,2048], tx_idx [n,2048]."""
+        if self.cfg is None:
+            raise _lib.MmimoError("LinkEngine.configure() has not been called")
+        K = self.cfg["n_ant"]
+        inject = inject or {}
+        rq = _lib.SdrRequest()
+        rq.n_frames, rq.seed, rq.frame_id0 = int(n_frames), int(seed) & (2 ** 64 - 1), int(frame_id0)
+        keep = []
+        if inject.get("rx_pos") is not None:
+            a = np.ascontiguousarray(np.asarray(inject["rx_pos"], dtype=np.float64).reshape(n_frames, 3)); keep.append(a)
+            rq.rx_pos = _ptr(a, C.c_double)
+        if inject.get("h_true") is not None:
+            a = _c64(inject["h_true"], (n_frames, K, N_SC)); keep.append(a)
+            rq.h_true = _ptr(a, C.c_float)
+        if inject.get("tx_idx") is not None:
+            a = np.ascontiguousarray(np.asarray(inject["tx_idx"], dtype=np.uint8).reshape(n_frames, N_SC)); keep.append(a)
+            rq.tx_idx = _ptr(a, C.c_uint8)
+        des = np.zeros(n_frames, dtype=np.float64)
+        dis = np.zeros(n_frames, dtype=np.float64)
+        _lib.check(self._lib, self._lib.mmimo_sdr_simulate(self._h, C.byref(rq), _ptr(des, C.c_double), _ptr(dis, C.c_double)))
+        return des, dis
+
     def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
                 inject=None, noise_unit=False):
         """Asynchronous: H2D of injected inputs + kernels, counters accumulate on the device until fetch().

@@ -161,3 +161,22 @@ def test_error_messages(engine):
     engine.configure(channel="injected")
     with pytest.raises(MmimoError):
         engine.simulate(1, 1, 10.0)
+
+
+def test_fused_sdr_matches_reference_snapshots(engine):
+    """mmimo_sdr_simulate vs the reference's SDR snapshot computation (tests/golden/full_size_extras.npz, generated from
+    main_beampatterns_plotting/sdr_mp.py's formulae on the unmodified reference classes), receiver positions and bits injected."""
+    g = load_golden("full_size_extras")
+    for i, ibo in enumerate(g["sdr_ibo"]):
+        engine.configure(n_ant=8, channel="los", pa="softlim", ibo_db=float(ibo))
+        idx = lo.bits_to_indices(g["sdr_bits"][i], 6)
+        des, dis = engine.sdr(1, inject=dict(rx_pos=g["sdr_pos"][i:i + 1], tx_idx=idx[None]))
+        assert abs(des[0] / g["sdr_desired"][i] - 1) < 2e-5
+        assert abs(dis[0] / g["sdr_distortion"][i] - 1) < 3e-4   # difference of nearly equal signals in fp32
+    # device RNG: SDR grows with the back-off (BASELINE config 4, "SDR vs IBO")
+    sdr = []
+    for ibo in (0.0, 3.0, 6.0):
+        engine.configure(n_ant=64, channel="los", pa="softlim", ibo_db=ibo)
+        des, dis = engine.sdr(64, seed=3)
+        sdr.append(10 * np.log10(np.mean(des / dis)))
+    assert sdr[0] < sdr[1] < sdr[2] and 10 < sdr[0] < 25
