@@ -205,6 +205,7 @@ __device__ __forceinline__ void load_tw1(Tw1& tw, const float2* __restrict__ tw4
 // measure the FMA-pipe and LSU-pipe demands separately).  SyncCta: the CTA of 256 threads runs one transform.
 struct SyncCta {
     static constexpr bool kExchange = true;
+    static constexpr bool kFakeTw2 = false;  // timing experiments only: pass-2 twiddles taken from registers
     __device__ __forceinline__ void x_begin() const {}
     __device__ __forceinline__ void x_sync() const { __syncthreads(); }
     __device__ __forceinline__ void x_end() const {}
@@ -252,7 +253,7 @@ __device__ __forceinline__ void fft4096(pf2 (&x)[16], pf2* __restrict__ bufA, pf
     radix16<S, false, false>(x);
 #pragma unroll
     for (int k = 1; k < 16; ++k) {
-        const float2 w = tw2[k * 16 + lo];
+        const float2 w = SYNC::kFakeTw2 ? tw1.at(k) : tw2[k * 16 + lo];
         x[k] = (S > 0) ? pcmulc(x[k], w.x, w.y) : pcmul(x[k], w.x, w.y);
     }
     sy.x_begin();

@@ -65,7 +65,9 @@ __device__ __forceinline__ pf2 pa_apply_pk(pf2 xp, const float p0, const float s
     const float p = fmaf(x.x, x.x, x.y * x.y);
     float g;
     if (KIND == PA_SOFT_LIMITER) {
-        g = fminf(1.0f, sqrt_p0 * rsqrtf(p));  // p <= p0 -> exactly 1 (p = 0 -> inf -> 1)
+        float rs;  // MUFU.RSQ without the denormal fix-up of rsqrtf (p = 0 or denormal -> inf -> gain 1)
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(p));
+        g = fminf(1.0f, sqrt_p0 * rs);  // p <= p0 -> exactly 1
     } else if (KIND == PA_RAPP) {
         const float r = __powf(p / p0, p1);
         g = __powf(1.0f + r, -0.5f / p1);

@@ -10,7 +10,11 @@
 #include "../../m_mimo_ofdm_with_nonlinear_pa_sim_b200/csrc/frame_kernel.cuh"
 using namespace mmimo;
 
+struct SyncFakeTw2 : SyncCta {  // full chain, but pass-2 twiddles from registers (wrong values, timing only)
+    static constexpr bool kFakeTw2 = true;
+};
 struct SyncNone {  // compute only: no data movement, no barriers
+    static constexpr bool kFakeTw2 = false;
     static constexpr bool kExchange = false;
     __device__ __forceinline__ void x_begin() const {}
     __device__ __forceinline__ void x_sync() const {}
@@ -18,6 +22,7 @@ struct SyncNone {  // compute only: no data movement, no barriers
 };
 
 struct SyncNoBar {  // data movement without any barrier (results are wrong; timing experiment only)
+    static constexpr bool kFakeTw2 = false;
     static constexpr bool kExchange = true;
     __device__ __forceinline__ void x_begin() const {}
     __device__ __forceinline__ void x_sync() const {}
@@ -27,7 +32,7 @@ struct SyncNoBar {  // data movement without any barrier (results are wrong; tim
 // MODE 4: full chain without barriers
 // MODE 0: full chain; 1: compute only; 2: exchange only (same addressing, 4 exchanges); 3: exchange without barriers
 template <int MODE>
-__global__ void __launch_bounds__(256, 2) k(float2* out, const float2* tw4096, const float2* tw256, int iters) {
+__global__ void __launch_bounds__(256, 2) k(float2* out, const float2* tw4096, const float2* tw256, int iters, int delay = 0) {
     extern __shared__ float2 smem[];
     pf2* bufA = reinterpret_cast<pf2*>(smem);
     pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
@@ -41,12 +46,23 @@ __global__ void __launch_bounds__(256, 2) k(float2* out, const float2* tw4096, c
 #pragma unroll
     for (int j = 0; j < 16; ++j) x[j] = pk((float)(t + j) * 1e-3f, (float)(t - j) * 1e-3f);
     const int hi = t >> 4, lo = t & 15;
+    if (delay > 0 && blockIdx.x >= gridDim.x / 2) {  // stagger the second CTA of every SM
+        const long long t0 = clock64();
+        while (clock64() - t0 < delay) {}
+    }
     for (int it = 0; it < iters; ++it) {
         if (MODE == 0) {
             fft4096<+1, true, false>(x, bufA, bufB, tw2, tw1, t);
 #pragma unroll
             for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
             fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
+        } else if (MODE == 5) {
+            fft4096<+1, true, false, SyncFakeTw2>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
+            fft4096<-1, false, true, SyncFakeTw2>(x, bufA, bufB, tw2, tw1, t);
 #pragma unroll
             for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
         } else if (MODE == 4) {
@@ -89,6 +105,67 @@ __global__ void __launch_bounds__(256, 2) k(float2* out, const float2* tw4096, c
 #pragma unroll
     for (int j = 0; j < 16; ++j) { const float2 v = unpk(x[j]); s.x += v.x; s.y += v.y; }
     if (s.x == 123.456f) out[0] = s;
+}
+
+// co-residency experiment: half of the CTAs run the butterflies only, the other half the exchanges only; each CTA
+// reports its own duration (clock64) and SM id.  cls: 0 = mixed, 1 = all compute, 2 = all exchange
+__global__ void __launch_bounds__(256, 2) kmix(long long* dur, int* smid, const float2* tw4096, const float2* tw256, int iters, int cls) {
+    extern __shared__ float2 smem[];
+    pf2* bufA = reinterpret_cast<pf2*>(smem);
+    pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
+    float2* tw2 = smem + 8192;
+    const int t = threadIdx.x;
+    tw2[t] = tw256[t];
+    Tw1 tw1;
+    load_tw1(tw1, tw4096, t);
+    __syncthreads();
+    pf2 x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = pk((float)(t + j) * 1e-3f, (float)(t - j) * 1e-3f);
+    const int hi = t >> 4, lo = t & 15;
+    const bool compute = cls == 1 || (cls == 0 && blockIdx.x < gridDim.x / 2);
+    const long long t0 = clock64();
+    if (compute) {
+        for (int it = 0; it < iters; ++it) {
+            fft4096<+1, true, false, SyncNone>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = pa_apply_pk<PA_SOFT_LIMITER>(x[j], 1.0f, 1.0f, 0.f);
+            fft4096<-1, false, true, SyncNone>(x, bufA, bufB, tw2, tw1, t);
+#pragma unroll
+            for (int j = 4; j < 12; ++j) x[j] = pmul(x[j - 4], pbc(1e-3f));
+        }
+    } else {
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+#pragma unroll
+                for (int k2 = 0; k2 < 16; ++k2) bufA[k2 * 256 + t] = x[k2];
+                __syncthreads();
+#pragma unroll
+                for (int n1 = 0; n1 < 16; ++n1) x[n1] = bufA[hi * 256 + n1 * 16 + lo];
+                {
+                    const int base = hi * 16 + (lo ^ hi);
+#pragma unroll
+                    for (int k2 = 0; k2 < 16; ++k2) bufB[k2 * 256 + base] = x[k2];
+                }
+                __syncthreads();
+                {
+                    const int base = hi * 256 + lo * 16;
+#pragma unroll
+                    for (int n0 = 0; n0 < 16; ++n0) x[n0] = bufB[base + (n0 ^ lo)];
+                }
+            }
+        }
+    }
+    const long long t1 = clock64();
+    float2 s = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { const float2 v = unpk(x[j]); s.x += v.x; s.y += v.y; }
+    if (t == 0) {
+        dur[blockIdx.x] = t1 - t0 + (s.x == 123.456f ? 1 : 0);
+        unsigned id; asm("mov.u32 %0, %%smid;" : "=r"(id));
+        smid[blockIdx.x] = (int)id;
+    }
 }
 
 template <int NCTA>
@@ -140,7 +217,7 @@ static void run_c(float2* d, const float2* t4, const float2* t2, int nsm) {
 }
 
 template <int MODE>
-static void run(const char* name, float2* d, const float2* t4, const float2* t2, int nsm, int per_sm) {
+static void run(const char* name, float2* d, const float2* t4, const float2* t2, int nsm, int per_sm, int delay = 0) {
     const int iters = 2000, smem = (8192 + 256) * 8 + (per_sm == 1 ? 110 * 1024 : 0);  // extra smem forces 1 CTA/SM
     cudaFuncSetAttribute(k<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaEvent_t e0, e1;
@@ -148,7 +225,7 @@ static void run(const char* name, float2* d, const float2* t4, const float2* t2,
     float best = 1e30f;
     for (int rep = 0; rep < 4; ++rep) {
         cudaEventRecord(e0);
-        k<MODE><<<nsm * per_sm, 256, smem>>>(d, t4, t2, iters);
+        k<MODE><<<nsm * per_sm, 256, smem>>>(d, t4, t2, iters, delay);
         cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         if (rep) best = fminf(best, ms);
@@ -176,6 +253,25 @@ int main() {
         run<2>("4 exchanges only (STS, bar, LDS)", d, d4, d2, nsm, per_sm);
         run<3>("4 exchanges, no barrier", d, d4, d2, nsm, per_sm);
         run<4>("full chain, no barrier", d, d4, d2, nsm, per_sm);
+    }
+    run<5>("full chain, pass-2 twiddles in regs", d, d4, d2, nsm, 1);
+    run<5>("full chain, pass-2 twiddles in regs", d, d4, d2, nsm, 2);
+    {
+        const int iters = 2000, smem = (8192 + 256) * 8, grid = nsm * 2;
+        cudaFuncSetAttribute(kmix, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        long long* ddur; int* dsm;
+        cudaMalloc(&ddur, grid * 8); cudaMalloc(&dsm, grid * 4);
+        std::vector<long long> dur(grid); std::vector<int> sm(grid);
+        for (int cls = 0; cls < 3; ++cls) {
+            for (int rep = 0; rep < 2; ++rep) kmix<<<grid, 256, smem>>>(ddur, dsm, d4, d2, iters, cls);
+            cudaMemcpy(dur.data(), ddur, grid * 8, cudaMemcpyDeviceToHost);
+            cudaMemcpy(sm.data(), dsm, grid * 4, cudaMemcpyDeviceToHost);
+            double a = 0, b = 0; int paired = 0;
+            for (int i = 0; i < grid / 2; ++i) { a += dur[i]; b += dur[i + grid / 2]; }
+            for (int i = 0; i < grid / 2; ++i) for (int j = grid / 2; j < grid; ++j) if (sm[i] == sm[j]) { ++paired; break; }
+            printf("co-residency cls %d (0 mixed, 1 all compute, 2 all exchange): first half %8.0f cycles/chain/CTA, second half %8.0f; %d of %d first-half CTAs share an SM with a second-half CTA  [%s]\n",
+                   cls, a / (grid / 2) / iters, b / (grid / 2) / iters, paired, grid / 2, cudaGetErrorString(cudaGetLastError()));
+        }
     }
     run_c<2>(d, d4, d2, nsm);
     run_c<3>(d, d4, d2, nsm);
