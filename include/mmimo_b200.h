@@ -151,6 +151,41 @@ typedef struct mmimo_sdr_request {
 } mmimo_sdr_request;
 int mmimo_sdr_simulate(mmimo_ctx* ctx, const mmimo_sdr_request* req, double* desired, double* distortion);
 
+/* Two-user Monte-Carlo frames, fused (BASELINE config 5): the frame loop of
+ * main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642 and multiuser_mp_prototype.py - per realisation one channel
+ * per user (MisoLosFd / MisoTwoPathFd / MisoRayleighFd / injected), multi-user MRT or zero-forcing precoding
+ * (antenna_array.py:202-257), array PA re-normalisation (:313-360), one array transmission carrying both users
+ * (modulation.py:373), per user: propagate over its channel, AWGN, AGC, then McncMuReceiver.receive with knowledge of the
+ * other user's bits (corrector.py:404-446) or - loop_single_user - the single-user McncReceiver of the script (:563-572).
+ * Arrays with a user axis are ordered [n_frames][2][...]; err is [2][n_iter+1].  NULL optional inputs = generated on the
+ * device (Philox keyed on (seed, 2*frame + user)). */
+enum { MMIMO_MU_MRT = 0, MMIMO_MU_ZF = 1 };
+typedef struct mmimo_mu_request {
+    int32_t n_frames;          /* channel realisations; each yields one frame per user */
+    int32_t n_iter;
+    int32_t precoding;         /* MMIMO_MU_MRT / MMIMO_MU_ZF */
+    int32_t loop_single_user;  /* 0: McncMuReceiver (corrector.py:348); 1: per-user single-user McncReceiver (MRT of its own channel) */
+    double snr_db;
+    uint64_t seed;
+    uint64_t frame_id0;
+    double usr_pos[2][3];      /* nominal position of each user (usr_pos_tup of the script); offsets +-rx_loc_var/2 on x and y */
+    const double* rx_pos;      /* [n_frames][2][3] or NULL */
+    const float* h;            /* c64 [n_frames][2][n_ant][n_sub_carr] or NULL */
+    const uint8_t* tx_idx;     /* [n_frames][2][n_sub_carr] or NULL */
+    const float* noise;        /* c64 [n_frames][2][n_sub_carr] or NULL */
+    const float* rx_eq_in;     /* c64 [n_frames][2][n_sub_carr]: equalised received signal; skips the transmission (receiver-only use) */
+} mmimo_mu_request;
+typedef struct mmimo_mu_result {
+    uint64_t* err;             /* [2][n_iter+1] (required) */
+    uint64_t bits_per_frame;
+    uint8_t* det;              /* [n_frames][2][n_iter+1][n_sub_carr] or NULL */
+    float* rx_eq;              /* c64 [n_frames][2][n_sub_carr] or NULL */
+    float* v;                  /* c64 [n_frames][2][n_ant][n_sub_carr] precoder per user or NULL (reference layout is [K,U,N_sc]) */
+    float* agc;                /* c64 [n_frames][2][n_sub_carr] or NULL */
+    float* pa_p0;              /* [n_frames] or NULL */
+} mmimo_mu_result;
+int mmimo_mu_link_simulate(mmimo_ctx* ctx, const mmimo_mu_request* req, mmimo_mu_result* res);
+
 /* number of kernels launched by this context so far (bench.py "gpu_launches") */
 uint64_t mmimo_launch_count(mmimo_ctx* ctx);
 

@@ -38,6 +38,17 @@ class SdrRequest(C.Structure):
                 ("rx_pos", c_d_p), ("h_true", c_f_p), ("tx_idx", c_u8_p)]
 
 
+class MuRequest(C.Structure):
+    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("precoding", C.c_int32), ("loop_single_user", C.c_int32),
+                ("snr_db", C.c_double), ("seed", C.c_uint64), ("frame_id0", C.c_uint64), ("usr_pos", (C.c_double * 3) * 2),
+                ("rx_pos", c_d_p), ("h", c_f_p), ("tx_idx", c_u8_p), ("noise", c_f_p), ("rx_eq_in", c_f_p)]
+
+
+class MuResult(C.Structure):
+    _fields_ = [("err", c_u64_p), ("bits_per_frame", C.c_uint64), ("det", c_u8_p), ("rx_eq", c_f_p), ("v", c_f_p),
+                ("agc", c_f_p), ("pa_p0", c_f_p)]
+
+
 class MmimoError(RuntimeError):
     pass
 
@@ -47,7 +58,7 @@ _LIB = None
 # every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
            "mmimo_set_stream", "mmimo_counters_to_device",
-           "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
+           "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
            "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
            "mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_array_transmit",
@@ -93,6 +104,8 @@ def load(build_if_missing: bool = True):
     lib.mmimo_link_enqueue.argtypes = [C.c_void_p, C.POINTER(SimRequest)]
     lib.mmimo_link_fetch.argtypes = [C.c_void_p, C.c_int32, c_u64_p, c_u64_p]
     lib.mmimo_sdr_simulate.argtypes = [C.c_void_p, C.POINTER(SdrRequest), c_d_p, c_d_p]
+    lib.mmimo_mu_link_simulate.argtypes = [C.c_void_p, C.POINTER(MuRequest), C.POINTER(MuResult)]
+    lib.mmimo_mu_link_simulate.restype = C.c_int
     lib.mmimo_launch_count.argtypes = [C.c_void_p]
     lib.mmimo_launch_count.restype = C.c_uint64
     lib.mmimo_profile.argtypes = [C.c_void_p, C.c_int]

@@ -52,10 +52,17 @@ struct FrameArgs {
     uint32_t* err_out;           // [F][I+1], or nullptr
     unsigned long long* err_total;  // [I+1] accumulated with atomics
     float2* rxeq_scratch;        // [gridDim.x][2048] per-CTA scratch for the equalised received signal (stays in L2)
+    // Two-user mode (MU instantiation only; corrector.py:348-489 McncMuReceiver, antenna_array.py:202-257): frames are
+    // receiver INSTANCES ordered (realisation, user); instance f ^ 1 is the other user of the same realisation.  Both
+    // sides use explicit precoders v = [inst][K][2048]; every array transmit sends own + other user
+    // (modulation.py:373), the other user's symbols being the TRUE ones in the receiver loop (corrector.py:437-440).
+    // loop_single_user != 0: the loop side models a single-user array instead (main_multiuser_mcnc_ber_vs_ebn0.py:563-572).
+    int loop_single_user;
 };
 
 constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048;
 constexpr int FRAME_SMEM_BYTES = FRAME_SMEM_FLOAT2 * 8 + 64 * 4;
+constexpr int FRAME_SMEM_BYTES_MU = FRAME_SMEM_BYTES + N_SC * 8;  // + scaled symbols of the other user
 
 // packed PA (distortion.py:9-19 soft limiter, :102-113 Rapp, :202-211 third order)
 template <int KIND>
@@ -92,7 +99,7 @@ __device__ __forceinline__ void antenna_chain(pf2 (&x)[16], pf2* bufA, pf2* bufB
     fft4096<-1, false, true>(x, bufA, bufB, tw2, tw1, t, SyncCta(), before_last_pass);
 }
 
-template <int PA>
+template <int PA, bool MU = false>
 __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a, const float2* __restrict__ tw4096,
                                                                const float2* __restrict__ tw256) {
     extern __shared__ float2 smem[];
@@ -104,6 +111,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
     // scratch (L2-resident) instead of 16 KB of shared memory, which leaves the L1 room for the channel rows
     float2* rxeq_s = a.rxeq_scratch + (size_t)blockIdx.x * N_SC;
     unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + 2048);
+    float2* symo_s = reinterpret_cast<float2*>(err_s + 64);  // MU only: scaled symbols of the other user
 
     const int t = threadIdx.x;
     tw2[t] = tw256[t];
@@ -115,22 +123,26 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
     for (int f = blockIdx.x; f < a.n_frames; f += gridDim.x) {
         const FrameScalars sc = a.scal[f * a.scal_fs];
         // ---- transmitted symbols -------------------------------------------------------------
-        uint32_t txw[2];
-        if (a.tx_idx) {
-            const uint8_t* p = a.tx_idx + (size_t)f * N_SC;
-            txw[0] = txw[1] = 0;
+        uint32_t txw[2], otw[2] = {0u, 0u};
+        auto load_tx = [&](const int g, uint32_t (&w)[2]) {  // 8 symbol values of this thread for instance g
+            if (a.tx_idx) {
+                const uint8_t* p = a.tx_idx + (size_t)g * N_SC;
+                w[0] = w[1] = 0;
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
-        } else {
-            uint32_t r[4];
-            const uint64_t fid = a.frame_id0 + f;
-            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
-                          (uint32_t)(a.seed >> 32), r);
-            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
-            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
-            txw[0] = r[0] & m4;
-            txw[1] = r[1] & m4;
-        }
+                for (int jp = 0; jp < 8; ++jp) w[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
+            } else {
+                uint32_t r[4];
+                const uint64_t fid = a.frame_id0 + g;
+                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
+                              (uint32_t)(a.seed >> 32), r);
+                const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+                const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+                w[0] = r[0] & m4;
+                w[1] = r[1] & m4;
+            }
+        };
+        load_tx(f, txw);
+        if (MU) load_tx(f ^ 1, otw);
         uint32_t curw[2] = {txw[0], txw[1]};  // symbols fed to the next array transmit
 
         for (int pass = 0; pass <= a.n_iter; ++pass) {
@@ -140,6 +152,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             const float2* __restrict__ Hm = sd.h_mac + f * sd.h_mac_fs;
             const float2* __restrict__ Hp = sd.v ? sd.v + f * sd.v_fs : sd.h_pre + f * sd.h_pre_fs;
             const bool explicit_v = sd.v != nullptr;
+            const bool two_usr = MU && !(a.loop_single_user && !first);
+            const float2* __restrict__ Ho = (MU && sd.v) ? sd.v + (f ^ 1) * sd.v_fs : nullptr;  // precoder rows of the other user
             const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
             const float sqrt_p0 = sqrtf(p0);
             {
@@ -150,6 +164,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
                     const float2 s = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
                     const float g = ss[p];
                     symn_s[p] = make_float2(s.x * g, s.y * g);
+                    if (MU) {
+                        const float2 o = qam_symbol(a.qam, (otw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                        symo_s[p] = make_float2(o.x * g, o.y * g);
+                    }
                 }
             }
             pf2 acc[8];
@@ -176,6 +194,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
                     for (int jp = 0; jp < 8; ++jp) {
                         const float2 s = symn_s[jp * 256 + t];
                         x[jp_to_j(jp)] = pcmul(rown[jp], s.x, s.y);
+                        if (MU && two_usr)  // modulation.py:373: sum over users of symbol * precoder
+                            x[jp_to_j(jp)] = pcfma(pk2(__ldg(Ho + (size_t)k * N_SC + jp * 256 + t)), pk2(symo_s[jp * 256 + t]), x[jp_to_j(jp)]);
                     }
                 } else {
 #pragma unroll
@@ -264,7 +284,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             const unsigned int e = err_s[t];
             err_s[t] = 0;
             if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
-            atomicAdd(&a.err_total[t], (unsigned long long)e);
+            atomicAdd(&a.err_total[t + (MU ? (f & 1) * 32 : 0)], (unsigned long long)e);  // MU: user 1 counts at [32..]
         }
         __syncthreads();
     }

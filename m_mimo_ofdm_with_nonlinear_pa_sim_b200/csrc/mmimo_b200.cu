@@ -13,6 +13,7 @@
 
 #include "../../include/mmimo_b200.h"
 #include "prep_kernels.cuh"
+#include "mu_kernels.cuh"
 #include "stage_kernels.cuh"
 
 using namespace mmimo;
@@ -327,4 +328,5 @@ extern "C" int mmimo_measure_fp32_peak(mmimo_ctx* c, double* tflops) {
 }
 
 #include "link_host.inl"
+#include "mu_host.inl"
 #include "stage_host.inl"

@@ -32,6 +32,10 @@ struct ChanArgs {
     uint32_t pos_stream;      // RNG_POS or a clean-run stream
     float2* h_out;            // [F][K][2048]
     int n_ant;
+    // multi-user scripts (main_multiuser_mcnc_ber_vs_ebn0.py:546-556): frame f belongs to user f % n_usr whose nominal
+    // position is rx0_tab[user]; here x and y are offset around their OWN nominal values (no cord_y quirk)
+    const double* rx0_tab;    // [n_usr][3] or nullptr
+    int n_usr;
 };
 
 __device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bool skip_att) {
@@ -53,9 +57,16 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
         uint32_t r[4];
         const uint64_t fid = a.frame_id0 + f;
         philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.pos_stream, 0u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
-        rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
-        rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
-        rx[2] = a.rx0[2];
+        if (a.rx0_tab) {
+            const double* n0 = a.rx0_tab + (size_t)((a.frame_id0 + f) % (uint64_t)a.n_usr) * 3;
+            rx[0] = n0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+            rx[1] = n0[1] + (u01(r[2], r[3]) - 0.5) * a.loc_var;
+            rx[2] = n0[2];
+        } else {
+            rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+            rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
+            rx[2] = a.rx0[2];
+        }
     }
     if (a.rx_pos_out && k == 0 && t < 3) a.rx_pos_out[f * 3 + t] = rx[t];
     const double dx = a.tx_pos[k * 3 + 0] - rx[0], dy = a.tx_pos[k * 3 + 1] - rx[1], dz = a.tx_pos[k * 3 + 2] - rx[2];

@@ -207,6 +207,58 @@ class LinkEngine:
         _lib.check(self._lib, self._lib.mmimo_sdr_simulate(self._h, C.byref(rq), _ptr(des, C.c_double), _ptr(dis, C.c_double)))
         return des, dis
 
+    def mu_simulate(self, n_frames, n_iter, snr_db, *, precoding="mrt", usr_pos=((212.0, 212.0, 1.5), (150.0, 250.0, 1.5)),
+                    loop_single_user=False, seed=0, frame_id0=0, inject=None, dumps=()):
+        """Fused two-user frames (main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642, corrector.py:348-489):
+        n_frames channel realisations, one frame per user each.  precoding "mrt" | "zf" (antenna_array.py:202-257).
+        inject: optional rx_pos [n,2,3], h [n,2,K,2048], tx_idx [n,2,2048], noise [n,2,2048], rx_eq_in [n,2,2048].
+        dumps: any of "det", "rx_eq", "v", "agc", "pa_p0".  Returns dict with err [2, n_iter+1], bits (per user)."""
+        if self.cfg is None:
+            raise _lib.MmimoError("LinkEngine.configure() has not been called")
+        K = self.cfg["n_ant"]
+        inject = inject or {}
+        n = int(n_frames)
+        rq = _lib.MuRequest()
+        rq.n_frames, rq.n_iter, rq.snr_db = n, int(n_iter), float(snr_db)
+        rq.precoding = {"mrt": 0, "zf": 1}[precoding]
+        rq.loop_single_user = 1 if loop_single_user else 0
+        rq.seed, rq.frame_id0 = int(seed) & (2 ** 64 - 1), int(frame_id0)
+        for u in range(2):
+            for i in range(3):
+                rq.usr_pos[u][i] = float(usr_pos[u][i])
+        keep = []
+        if inject.get("rx_pos") is not None:
+            a = np.ascontiguousarray(np.asarray(inject["rx_pos"], dtype=np.float64).reshape(n, 2, 3)); keep.append(a)
+            rq.rx_pos = _ptr(a, C.c_double)
+        if inject.get("h") is not None:
+            a = _c64(inject["h"], (n, 2, K, N_SC)); keep.append(a)
+            rq.h = _ptr(a, C.c_float)
+        if inject.get("tx_idx") is not None:
+            a = np.ascontiguousarray(np.asarray(inject["tx_idx"], dtype=np.uint8).reshape(n, 2, N_SC)); keep.append(a)
+            rq.tx_idx = _ptr(a, C.c_uint8)
+        for key in ("noise", "rx_eq_in"):
+            if inject.get(key) is not None:
+                a = _c64(inject[key], (n, 2, N_SC)); keep.append(a)
+                setattr(rq, key, _ptr(a, C.c_float))
+        rs = _lib.MuResult()
+        err = np.zeros((2, int(n_iter) + 1), dtype=np.uint64)
+        rs.err = _ptr(err, C.c_uint64)
+        out = {}
+        if "det" in dumps:
+            out["det"] = np.zeros((n, 2, int(n_iter) + 1, N_SC), dtype=np.uint8); rs.det = _ptr(out["det"], C.c_uint8)
+        if "rx_eq" in dumps:
+            out["rx_eq"] = np.zeros((n, 2, N_SC), dtype=np.complex64); rs.rx_eq = _ptr(out["rx_eq"], C.c_float)
+        if "v" in dumps:
+            out["v"] = np.zeros((n, 2, K, N_SC), dtype=np.complex64); rs.v = _ptr(out["v"], C.c_float)
+        if "agc" in dumps:
+            out["agc"] = np.zeros((n, 2, N_SC), dtype=np.complex64); rs.agc = _ptr(out["agc"], C.c_float)
+        if "pa_p0" in dumps:
+            out["pa_p0"] = np.zeros(n, dtype=np.float32); rs.pa_p0 = _ptr(out["pa_p0"], C.c_float)
+        _lib.check(self._lib, self._lib.mmimo_mu_link_simulate(self._h, C.byref(rq), C.byref(rs)))
+        out["err"] = err
+        out["bits"] = np.full(2, n * int(rs.bits_per_frame), dtype=np.uint64)
+        return out
+
     def enqueue(self, n_frames, n_iter, snr_db, *, seed=0, frame_id0=0, incl_clean_run=False, csi_eps=0.0,
                 inject=None, noise_unit=False):
         """Asynchronous: H2D of injected inputs + kernels, counters accumulate on the device until fetch().

@@ -554,6 +554,43 @@ def frame_distorted(cfg: LinkConfig, real: Realisation, tx_idx, noise_fd, n_iter
     return det, err
 
 
+def mu_realisation(cfg: LinkConfig, h_list, precoding="mrt"):
+    """Two-user realisation: multi-user precoder (antenna_array.py:202-257), array PA parameters (:313-360) and the
+    per-user AGC / noise scalers of main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:580-622 (= corrector.py:374-400).
+    Returns dict(v [U,K,N_sc], pa, alpha_k [K], agc [U,N_sc], noise_scaler [U])."""
+    v = precoding_mu_mrt(h_list, cfg.n_sub_carr) if precoding == "mrt" else precoding_mu_zf(h_list, cfg.n_sub_carr)
+    ak = per_antenna_alpha(cfg, v)
+    agc = np.stack([np.sum(ak[:, None] * take_data_sc(h_list[u], cfg.n_sub_carr) * v[u], axis=0) for u in range(len(h_list))])
+    return dict(v=v, pa=pa_params(cfg, v), alpha_k=ak, agc=agc,
+                noise_scaler=np.mean(np.power(np.abs(agc), 2), axis=1))
+
+
+def mu_frame(cfg: LinkConfig, h_list, tx_idx, noise_fd, n_iter_max, precoding="mrt", loop_single_user=False, real=None):
+    """One two-user frame (script :624-642): one array transmission carrying both users, per user propagate over its
+    channel, add noise (noise_fd [U, n_fft], already scaled; None = noise free), AGC, McncMuReceiver.receive
+    (corrector.py:404-446) or - loop_single_user - a single-user McncReceiver on the user's own channel (:563-572).
+    Returns dict(rx_eq [U,N_sc], det [U, n_iter_max+1, N_sc], err [U, n_iter_max+1])."""
+    real = real or mu_realisation(cfg, h_list, precoding)
+    tx_idx = np.asarray(tx_idx)
+    x = array_transmit(cfg, tx_idx, real["v"], real["pa"])
+    n_usr = len(h_list)
+    rx_eq, det, err = [], [], []
+    for u in range(n_usr):
+        rx = np.sum(x * h_list[u], axis=0)
+        if noise_fd is not None:
+            rx = rx + noise_fd[u]
+        y = rx[cfg.bins] / real["agc"][u]
+        if loop_single_user:
+            su = make_realisation(cfg, h_list[u])
+            d = mcnc_receive(cfg, y, su.h_loop, su.v, su.pa, su.ak_hk_vk_agc, n_iter_max)
+        else:
+            d = mcnc_receive(cfg, y, h_list[u], real["v"], real["pa"], real["agc"][u], n_iter_max,
+                             other_usr_idx=tx_idx[1 - u], usr_idx=u)
+        rx_eq.append(y); det.append(d)
+        err.append(count_bit_errors(tx_idx[u], d))
+    return dict(rx_eq=np.stack(rx_eq), det=np.stack(det), err=np.array(err, dtype=np.int64))
+
+
 def frame_clean(cfg: LinkConfig, real: Realisation, tx_idx, noise_fd):
     """Clean ("no distortion") loop body, mp_model.py:158-173.  FFT(IFFT(x)) == x, so the whole chain is
     precode -> channel -> noise -> /hk_vk_agc -> detect (the final IFFT/+CP/FFT of :166-169 cancels)."""
