@@ -131,6 +131,14 @@ int mmimo_set_ibo(mmimo_ctx* ctx, double ibo_db);
 int mmimo_link_simulate(mmimo_ctx* ctx, const mmimo_sim_request* req, mmimo_sim_result* res);
 int mmimo_link_enqueue(mmimo_ctx* ctx, const mmimo_sim_request* req);
 int mmimo_link_fetch(mmimo_ctx* ctx, int32_t n_iter, uint64_t* err, uint64_t* clean_err);
+/* Multi-point batch: n_points * frames_per_point frames in one pass of the link pipeline; point p owns frames
+ * [p * frames_per_point, (p + 1) * frames_per_point) of the batch (global frame ids base->frame_id0 + index) and runs at
+ * snr_db[p] / ibo_db[p] (NULL = the value of `base` / of the configured link for every point).  Replaces the inner
+ * (IBO, Eb/N0) double loop of main_mp_clipping_noise_cancellation/main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:116-150
+ * and the point loops of ..._ber_vs_ebn0.py:108-140 / ..._ber_vs_ibo.py.  base->n_frames is ignored;
+ * err is [n_points][n_iter+1]. */
+int mmimo_link_sweep(mmimo_ctx* ctx, const mmimo_sim_request* base, int32_t n_points, int32_t frames_per_point,
+                     const double* snr_db, const double* ibo_db, uint64_t* err);
 /* stream-ordered copy of the 65 uint64 device counters ([0..63] bit errors after iteration i, [64] clean run)
  * into caller-owned DEVICE memory - the buffer handed to the NCCL all-reduce that replaces the shared
  * multiprocessing.Array accumulation of mp_model.py:172-173,221-222; clear != 0 zeroes the counters after the copy */

@@ -58,7 +58,7 @@ _LIB = None
 # every symbol include/mmimo_b200.h declares (tests/test_abi.py checks the header against this list)
 EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
            "mmimo_set_stream", "mmimo_counters_to_device",
-           "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
+           "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_sweep", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
            "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
            "mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_array_transmit",
@@ -106,6 +106,8 @@ def load(build_if_missing: bool = True):
     lib.mmimo_sdr_simulate.argtypes = [C.c_void_p, C.POINTER(SdrRequest), c_d_p, c_d_p]
     lib.mmimo_mu_link_simulate.argtypes = [C.c_void_p, C.POINTER(MuRequest), C.POINTER(MuResult)]
     lib.mmimo_mu_link_simulate.restype = C.c_int
+    lib.mmimo_link_sweep.argtypes = [C.c_void_p, C.POINTER(SimRequest), C.c_int32, C.c_int32, c_d_p, c_d_p, c_u64_p]
+    lib.mmimo_link_sweep.restype = C.c_int
     lib.mmimo_launch_count.argtypes = [C.c_void_p]
     lib.mmimo_launch_count.restype = C.c_uint64
     lib.mmimo_profile.argtypes = [C.c_void_p, C.c_int]

@@ -123,6 +123,7 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     pa.avg_symbol_power = avg_symbol_power(cfg.constel_size);
     pa.avg_sample_power = pa.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
     pa.snr_lin = pow(10.0, rq->snr_db / 10.0);
+    pa.snr_lin_tab = c->sweep.snr_lin; pa.ibo_lin_tab = c->sweep.ibo_lin; pa.fpp = c->sweep.fpp; pa.frame0 = (long long)c0;
     prof_begin(c, PROF_PREP);
     k_prep_realisation<<<n, 256, 0, c->stream>>>(pa);
     prof_end(c);
@@ -249,7 +250,8 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.rx_eq_out = want_rxeq ? c->rx_eq.as<float2>() : nullptr;
         fa.corr_out = want_corr ? c->corr.as<float2>() : nullptr;
         fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
-        fa.err_total = counters;
+        fa.err_total = c->sweep.fpp ? c->sweep.counters : counters;
+        fa.fpp = c->sweep.fpp; fa.frame0 = (long long)c0;
         if (c->rxeq_scr.reserve((size_t)8 * c->n_sm * N_SC * 8)) return 1;  // >= the largest grid launch_frame uses
         fa.rxeq_scratch = c->rxeq_scr.as<float2>();
         const int grid = n;
@@ -316,6 +318,48 @@ extern "C" int mmimo_link_simulate(mmimo_ctx* c, const mmimo_sim_request* rq, mm
     if (run_link(c, rq, rs)) return 1;
     rs->bits_per_frame = (uint64_t)(2 * log2_side(c->cfg.constel_size)) * N_SC;
     return mmimo_link_fetch(c, rq->n_iter, rs->err, rs->clean_err);
+}
+
+// Multi-point batch: n_points * frames_per_point frames in ONE pass of the link pipeline, point p = frames
+// [p * fpp, (p + 1) * fpp) with its own SNR and IBO; per-point counters.  This is the inner double loop of
+// main_mp_clipping_noise_cancellation/main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:116-150 (16 IBO x 27 Eb/N0 points
+// of <= 407 frames each) and of ..._ber_vs_ebn0.py / ..._ber_vs_ibo.py without a launch (and a partly filled last wave of
+// CTAs) per point.
+extern "C" int mmimo_link_sweep(mmimo_ctx* c, const mmimo_sim_request* base, int32_t n_points, int32_t frames_per_point,
+                                const double* snr_db, const double* ibo_db, uint64_t* err) {
+    if (!c || !base || !err) return fail("mmimo_link_sweep: NULL argument");
+    if (!c->configured) return fail("mmimo_link_sweep: context not configured (call mmimo_configure)");
+    if (n_points <= 0 || frames_per_point <= 0) return fail("mmimo_link_sweep: n_points and frames_per_point must be positive");
+    if ((long long)n_points * frames_per_point > 0x7fffffffLL) return fail("mmimo_link_sweep: too many frames in one batch");
+    if (base->incl_clean_run) return fail("mmimo_link_sweep: incl_clean_run is not supported in a multi-point batch");
+    if (ibo_db && c->cfg.receiver_kind != MMIMO_RX_MCNC) return fail("mmimo_link_sweep: a per-point IBO needs the MCNC receiver");
+    if (base->n_iter < 0 || base->n_iter > 62) return fail("mmimo_link_sweep: n_iter must be 0..62");
+    CK(cudaSetDevice(c->device));
+    const size_t np_ = (size_t)n_points;
+    if (c->sweep_tab.reserve(2 * np_ * 8) || c->sweep_cnt.reserve(np_ * 64 * 8)) return 1;
+    std::vector<double> tab(2 * np_);
+    for (size_t i = 0; i < np_; ++i) {
+        tab[i] = pow(10.0, (snr_db ? snr_db[i] : base->snr_db) / 10.0);
+        tab[np_ + i] = pow(10.0, (ibo_db ? ibo_db[i] : c->cfg.ibo_db) / 10.0);
+    }
+    CK(cudaMemcpyAsync(c->sweep_tab.p, tab.data(), 2 * np_ * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // `tab` goes out of scope
+    CK(cudaMemsetAsync(c->sweep_cnt.p, 0, np_ * 64 * 8, c->stream));
+    mmimo_sim_request rq = *base;
+    rq.n_frames = n_points * frames_per_point;
+    c->sweep.snr_lin = c->sweep_tab.as<double>();
+    c->sweep.ibo_lin = c->sweep_tab.as<double>() + np_;
+    c->sweep.fpp = frames_per_point;
+    c->sweep.counters = c->sweep_cnt.as<unsigned long long>();
+    const int rc = run_link(c, &rq, nullptr);
+    c->sweep = mmimo_ctx::Sweep();
+    if (rc) return rc;
+    std::vector<unsigned long long> h(np_ * 64);
+    CK(cudaMemcpyAsync(h.data(), c->sweep_cnt.p, np_ * 64 * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    for (size_t p = 0; p < np_; ++p)
+        for (int i = 0; i <= base->n_iter; ++i) err[p * (base->n_iter + 1) + i] = h[p * 64 + i];
+    return 0;
 }
 
 template <int PA>

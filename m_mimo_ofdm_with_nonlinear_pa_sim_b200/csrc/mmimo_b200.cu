@@ -69,6 +69,9 @@ struct mmimo_ctx {
     DevBuf h_true, h_loop, csi_nz, rxeq_scr, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
+    // multi-point batch in flight (mmimo_link_sweep): device tables of 10^(x/10) per point, 64 counters per point
+    struct Sweep { const double* snr_lin = nullptr; const double* ibo_lin = nullptr; int fpp = 0; unsigned long long* counters = nullptr; } sweep;
+    DevBuf sweep_tab, sweep_cnt;
     // stage-op scratch
     DevBuf s_a, s_b, s_c, s_d;
     // optional per-kernel CUDA-event timing (mmimo_profile)

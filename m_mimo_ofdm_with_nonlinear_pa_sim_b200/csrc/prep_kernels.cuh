@@ -112,6 +112,10 @@ struct PrepArgs {
     double avg_symbol_power;   // 42 for 64-QAM (modulation.py:218)
     double avg_sample_power;   // avg_symbol_power * n_sub_carr / n_fft (modulation.py:424)
     double snr_lin;            // 10^(snr_db/10)
+    // multi-point batches (mmimo_link_sweep): frame f of this launch belongs to sweep point (frame0 + f) / fpp, whose
+    // IBO / SNR replace the scalars above
+    const double* snr_lin_tab; const double* ibo_lin_tab;
+    int fpp; long long frame0;
 };
 
 __device__ __forceinline__ double block_sum_256(double v, double* red_s, int t) {
@@ -132,6 +136,12 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
     __shared__ double vkpow_s[MAX_ANT];
     __shared__ double red_s[8];
     const int f = blockIdx.x, t = threadIdx.x, K = a.n_ant;
+    double ibo_lin = a.ibo_lin, snr_lin = a.snr_lin;
+    if (a.fpp) {
+        const long long pt = (a.frame0 + f) / a.fpp;
+        if (a.ibo_lin_tab) ibo_lin = a.ibo_lin_tab[pt];
+        if (a.snr_lin_tab) snr_lin = a.snr_lin_tab[pt];
+    }
     const float2* __restrict__ H = a.h_loop + f * a.h_fs;
     const float2* __restrict__ Vin = a.v_in ? a.v_in + (size_t)f * K * N_SC : nullptr;
     float2* Vout = a.v_out ? a.v_out + (size_t)f * K * N_SC : nullptr;
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
         for (int w = 0; w < 8; ++w) s += (double)part_s[t][w];
         vkpow_s[t] = s;
         // mp_model.py:315-317 + modulation.py:178-189
-        const double g2 = a.ibo_lin * (double)N_SC / (s * (double)K);
+        const double g2 = ibo_lin * (double)N_SC / (s * (double)K);
         const double g = sqrt(g2);
         const double al = 1.0 - exp(-g2) + (1.7724538509055160273 * g * 0.5) * erfc(g);
         alpha_s[t] = (float)al;
@@ -223,14 +233,14 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a) {
         const double gain = tot / ((double)K * N_SC);           // antenna_array.py:328-341
         const double avg = a.avg_sample_power * gain;
         FrameScalars sc;
-        const double p0_tx = (a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / avg : a.ibo_lin * avg;  // distortion.py:37,228
+        const double p0_tx = (a.pa_kind == PA_TOI) ? (1.0 / ibo_lin) / avg : ibo_lin * avg;  // distortion.py:37,228
         // CNC loop PA: avg_samp_pow = avg_symbol_power * n_sub_carr / n_fft (corrector.py:34-35)
-        const double p0_cnc = (a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / a.avg_sample_power : a.ibo_lin * a.avg_sample_power;
+        const double p0_cnc = (a.pa_kind == PA_TOI) ? (1.0 / ibo_lin) / a.avg_sample_power : ibo_lin * a.avg_sample_power;
         sc.pa_p0_tx = (float)p0_tx;
         sc.pa_p0_loop = (float)(a.is_mcnc ? p0_tx : p0_cnc);
         // noise.py:64-66: component std = 0.5*sqrt(2 P / snr), P = avg_symbol_power * noise_scaler
-        sc.noise_sigma = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_agc / N_SC) / a.snr_lin));
-        sc.noise_sigma_clean = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_hv / N_SC) / a.snr_lin));
+        sc.noise_sigma = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_agc / N_SC) / snr_lin));
+        sc.noise_sigma_clean = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_hv / N_SC) / snr_lin));
         a.scal[f] = sc;
     }
 }

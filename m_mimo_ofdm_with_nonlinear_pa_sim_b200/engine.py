@@ -207,6 +207,25 @@ class LinkEngine:
         _lib.check(self._lib, self._lib.mmimo_sdr_simulate(self._h, C.byref(rq), _ptr(des, C.c_double), _ptr(dis, C.c_double)))
         return des, dis
 
+    def sweep(self, snr_db, ibo_db, frames_per_point, n_iter, *, seed=0, frame_id0=0, csi_eps=0.0):
+        """Multi-point batch (mmimo_link_sweep): point p runs frames [p*fpp, (p+1)*fpp) of one batch at snr_db[p] /
+        ibo_db[p] (either may be None = the configured value / a scalar broadcast).  Returns err [n_points, n_iter+1].
+        The inner (IBO, Eb/N0) loops of main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:116-150 in one launch chain."""
+        if self.cfg is None:
+            raise _lib.MmimoError("LinkEngine.configure() has not been called")
+        snr = None if snr_db is None else np.atleast_1d(np.asarray(snr_db, dtype=np.float64))
+        ibo = None if ibo_db is None else np.atleast_1d(np.asarray(ibo_db, dtype=np.float64))
+        n_pts = max(len(snr) if snr is not None else 1, len(ibo) if ibo is not None else 1)
+        if snr is not None:
+            snr = np.ascontiguousarray(np.broadcast_to(snr, (n_pts,)))
+        if ibo is not None:
+            ibo = np.ascontiguousarray(np.broadcast_to(ibo, (n_pts,)))
+        rq, _keep = self._request(0, n_iter, 0.0 if snr is None else float(snr[0]), seed, frame_id0, False, csi_eps, None)
+        err = np.zeros((n_pts, int(n_iter) + 1), dtype=np.uint64)
+        _lib.check(self._lib, self._lib.mmimo_link_sweep(self._h, C.byref(rq), n_pts, int(frames_per_point),
+                                                         _ptr(snr, C.c_double), _ptr(ibo, C.c_double), _ptr(err, C.c_uint64)))
+        return err
+
     def mu_simulate(self, n_frames, n_iter, snr_db, *, precoding="mrt", usr_pos=((212.0, 212.0, 1.5), (150.0, 250.0, 1.5)),
                     loop_single_user=False, seed=0, frame_id0=0, inject=None, dumps=()):
         """Fused two-user frames (main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642, corrector.py:348-489):

@@ -180,3 +180,23 @@ def test_fused_sdr_matches_reference_snapshots(engine):
         des, dis = engine.sdr(64, seed=3)
         sdr.append(10 * np.log10(np.mean(des / dis)))
     assert sdr[0] < sdr[1] < sdr[2] and 10 < sdr[0] < 25
+
+
+def test_multi_point_sweep_equals_point_by_point(engine):
+    """mmimo_link_sweep: one batch carrying several (Eb/N0, IBO) points gives exactly the counters of separate runs of the
+    same global frame ids (the RNG is keyed on the frame id, the PA / AGC / noise scalers are per frame)"""
+    engine.configure(n_ant=16, channel="los", pa="softlim", ibo_db=1.0, receiver="mcnc")
+    snr = np.array([14.0, 18.0, 22.0, 18.0])
+    ibo = np.array([0.0, 0.0, 3.0, 6.0])
+    fpp, n_iter = 24, 3
+    err = engine.sweep(snr, ibo, fpp, n_iter, seed=77, frame_id0=1000)
+    for p in range(len(snr)):
+        engine.set_ibo(float(ibo[p]))
+        ref = engine.simulate(fpp, n_iter, float(snr[p]), seed=77, frame_id0=1000 + p * fpp)["err"]
+        assert np.array_equal(err[p], ref), (p, err[p], ref)
+    assert err[1, 0] < err[0, 0]          # more Eb/N0, fewer errors
+    # IBO left at the configured value when no table is given
+    engine.set_ibo(2.0)
+    e2 = engine.sweep(snr[:2], None, fpp, n_iter, seed=5)
+    r0 = engine.simulate(fpp, n_iter, float(snr[0]), seed=5, frame_id0=0)["err"]
+    assert np.array_equal(e2[0], r0)

@@ -48,9 +48,58 @@ def run_sweep(eng, a, rank=0, world=1, exchange=None):
     return ax, rows, frames
 
 
+def run_fixed_ber(eng, a, rank=0, world=1, exchange=None):
+    """Required Eb/N0 for a target BER versus IBO (main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:99-180): BER on the
+    whole IBO x Eb/N0 grid, every IBO row as ONE multi-point batch per round (LinkEngine.sweep), the reference's stopping
+    rule per (point, iteration), then interp1d(BER -> Eb/N0) per IBO and iteration (inf where the target is not crossed).
+    Returns (ibo axis, req_ebn0 [n_iter+1, n_ibo], ber [n_ibo, n_ebn0, n_iter+1], frames)."""
+    from scipy import interpolate
+
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200.parallel import shard_range
+    ebn0s, ibos = axis(a.ebn0), axis(a.ibo)
+    bits_frame = int(math.log2(a.constel)) * 2048
+    snr = 10 * np.log10(10 ** (ebn0s / 10) * math.log2(a.constel))
+    n_it = a.n_iter + 1
+    ber = np.full((len(ibos), len(ebn0s), n_it), np.nan)
+    frames = 0
+    fpp = max(world, (a.frames_per_step // world) * world)  # frames per point and round, split evenly over the ranks
+    for i, ibo in enumerate(ibos):
+        err = np.zeros((len(ebn0s), n_it)); bits = np.zeros((len(ebn0s), n_it))
+        rnd = 0
+        while True:
+            active = (err < a.err_min) & (bits < a.bits_max)          # mp_model.py:181-187 per result slot
+            if not active.any():
+                break
+            pts = np.nonzero(active.any(axis=1))[0]
+            lo, cnt = shard_range(fpp, rank, world)
+            # every rank runs its share of each point's frames; ids are unique per (ibo, round, point, frame)
+            fid0 = ((i * 4096 + rnd) * len(ebn0s)) * fpp
+            e = np.zeros((len(pts), n_it))
+            if cnt > 0:
+                e = eng.sweep(snr[pts], np.full(len(pts), ibo), cnt, a.n_iter, seed=a.seed, frame_id0=fid0 + lo * len(pts),
+                              csi_eps=a.csi_eps).astype(np.float64)
+            if exchange is not None:
+                e = exchange.allreduce(e.ravel()).reshape(len(pts), n_it)
+            for j, p in enumerate(pts):
+                err[p] += np.where(active[p], e[j], 0)
+                bits[p] += np.where(active[p], fpp * bits_frame, 0)
+            frames += fpp * len(pts)
+            rnd += 1
+        ber[i] = err / np.maximum(bits, 1)
+    req = np.full((n_it, len(ibos)), np.inf)
+    for it in range(n_it):
+        for i in range(len(ibos)):
+            try:
+                req[it, i] = float(interpolate.interp1d(ber[i, :, it], ebn0s)(a.target_ber))
+            except ValueError:
+                pass  # target not crossed on this Eb/N0 range: the reference stores inf (script :171-175)
+    return ibos, req, ber, frames
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--sweep", choices=["ebn0", "ibo"], default="ebn0")
+    ap.add_argument("--sweep", choices=["ebn0", "ibo", "fixed-ber"], default="ebn0")
+    ap.add_argument("--target-ber", type=float, default=1e-2)
     ap.add_argument("--ebn0", default="5:20:0.5")
     ap.add_argument("--ibo", default="0")
     ap.add_argument("--n-ant", type=int, default=64)
@@ -80,7 +129,10 @@ def main():
     eng = LinkEngine(local)
     eng.configure(constel_size=a.constel, n_ant=a.n_ant, pa=a.pa, ibo_db=axis(a.ibo)[0], channel=a.channel, receiver=a.receiver)
     t0 = time.time()
-    ax, rows, frames = run_sweep(eng, a, rank, world, exchange)
+    if a.sweep == "fixed-ber":
+        ax, rows, _ber, frames = run_fixed_ber(eng, a, rank, world, exchange)
+    else:
+        ax, rows, frames = run_sweep(eng, a, rank, world, exchange)
     dt = time.time() - t0
     if rank == 0:
         data = [list(ax)] + [list(r) for r in rows]
