@@ -231,6 +231,11 @@ int mmimo_pa_process(mmimo_ctx* ctx, const mmimo_pa_desc* pa, size_t n, const fl
 int mmimo_qam_map(mmimo_ctx* ctx, const mmimo_modem_desc* m, size_t n_sym, const uint8_t* bits, float* symbols);
 /* Modem.symbol_detection (:138-146) / demodulate (:63-77): nearest points (symbols, may be NULL) and their bits (may be NULL) */
 int mmimo_qam_detect(mmimo_ctx* ctx, const mmimo_modem_desc* m, size_t n_sym, const float* in, float* symbols, uint8_t* bits);
+/* modulation.soft_decoding / OfdmQamModem.soft_detection_llr (modulation.py:29-59, :407-417): exact bit LLRs
+ * log(sum_{bit=1} e^{-|y-c|^2/nv} / sum_{bit=0} e^{...}), MSB of each symbol first, +inf where the denominator underflows;
+ * noise_var holds 1 value (all symbols) or n_sym values; llr is [n_sym * log2(constel)] doubles */
+int mmimo_qam_soft_llr(mmimo_ctx* ctx, const mmimo_modem_desc* m, size_t n_sym, const float* in, const double* noise_var,
+                       size_t n_noise_var, double* llr);
 /* AntennaArray.transmit (antenna_array.py:58-140) = Transceiver.transmit (transceiver.py:98-174) for n_ant antennas that
  * share one modem description and one PA (pa == NULL: no impairment).
  *   bits     [n_users][n_sub_carr * log2(constel)]

@@ -26,7 +26,7 @@ class PaDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("p0", C.c_double), ("p1", C.c_double)]
 
 
-STAGE_EXPORTS = ["mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_array_transmit",
+STAGE_EXPORTS = ["mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
                  "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
                  "mmimo_channel_geometric", "mmimo_channel_fspl", "mmimo_channel_random_paths", "mmimo_precoding",
                  "mmimo_agc", "mmimo_cnc_receive", "mmimo_mcnc_receive"]
@@ -39,6 +39,7 @@ def bind(lib):
     lib.mmimo_pa_process.argtypes = [vp, pd, sz, c_f_p, c_f_p]
     lib.mmimo_qam_map.argtypes = [vp, md, sz, c_u8_p, c_f_p]
     lib.mmimo_qam_detect.argtypes = [vp, md, sz, c_f_p, c_f_p, c_u8_p]
+    lib.mmimo_qam_soft_llr.argtypes = [vp, md, sz, c_f_p, c_d_p, sz, c_d_p]
     lib.mmimo_array_transmit.argtypes = [vp, md, pd, i, i, c_u8_p, c_f_p, i, c_f_p, c_f_p]
     lib.mmimo_ofdm_demodulate.argtypes = [vp, md, c_f_p, c_f_p, c_u8_p]
     lib.mmimo_propagate.argtypes = [vp, i, i, c_f_p, c_f_p, i, c_f_p]
@@ -120,6 +121,15 @@ class StageOps:
         bits = np.empty(s.size * bps, dtype=np.uint8) if want_bits else None
         self._call(self._lib.mmimo_qam_detect, C.byref(md), s.size, _p(s, C.c_float), _p(sym, C.c_float), _p(bits, C.c_uint8))
         return (sym.astype(np.complex128) if want_symbols else None, bits.view(np.int8) if want_bits else None)
+
+    def qam_soft_llr(self, md, symbols, noise_var):
+        """modulation.soft_decoding (modulation.py:29-59): float64 LLRs, MSB of each symbol first"""
+        s = _c64(symbols).reshape(-1)
+        nv = np.ascontiguousarray(np.atleast_1d(np.asarray(noise_var, dtype=np.float64)).reshape(-1))
+        bps = int(np.log2(md.constel_size))
+        out = np.empty(s.size * bps, dtype=np.float64)
+        self._call(self._lib.mmimo_qam_soft_llr, C.byref(md), s.size, _p(s, C.c_float), _p(nv, C.c_double), nv.size, _p(out, C.c_double))
+        return out
 
     def array_transmit(self, md, pa, n_ant, n_users, bits, precoder, skip_dist=False, time_domain=False, per_user=False,
                        return_both=False):

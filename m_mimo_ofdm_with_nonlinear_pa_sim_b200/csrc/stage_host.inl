@@ -179,6 +179,27 @@ extern "C" int mmimo_qam_detect(mmimo_ctx* c, const mmimo_modem_desc* m, size_t 
     return 0;
 }
 
+extern "C" int mmimo_qam_soft_llr(mmimo_ctx* c, const mmimo_modem_desc* m, size_t n_sym, const float* in, const double* noise_var,
+                                  size_t n_noise_var, double* llr) {
+    STAGE_PROLOGUE(c);
+    int bps; Qam q;
+    if (check_modem(m, &bps, &q)) return 1;
+    if (!in || !noise_var || !llr) return fail("mmimo_qam_soft_llr: NULL buffer");
+    if (n_noise_var != 1 && n_noise_var != n_sym) return fail("mmimo_qam_soft_llr: noise_var must hold 1 or n_sym values");
+    if (n_sym == 0) return 0;
+    if (ar.begin(Arena::pad(n_sym * 8) + Arena::pad(n_noise_var * 8) + Arena::pad(n_sym * bps * 8))) return 1;
+    float2* din = ar.get<float2>(n_sym);
+    double* dnv = ar.get<double>(n_noise_var);
+    double* dllr = ar.get<double>(n_sym * bps);
+    CK(cudaMemcpyAsync(din, in, n_sym * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(dnv, noise_var, n_noise_var * 8, cudaMemcpyHostToDevice, c->stream));
+    k_soft_llr<<<nblk(n_sym), 256, 0, c->stream>>>(din, dnv, n_noise_var, dllr, n_sym, q, m->constel_scale, bps);
+    c->launches++;
+    CK(cudaMemcpyAsync(llr, dllr, n_sym * bps * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
 extern "C" int mmimo_array_transmit(mmimo_ctx* c, const mmimo_modem_desc* m, const mmimo_pa_desc* pa, int n_ant, int n_users,
                                     const uint8_t* bits, const float* precoder, int flags, float* out, float* out_clean) {
     STAGE_PROLOGUE(c);

@@ -60,6 +60,33 @@ __global__ void k_detect(const float2* __restrict__ in, uint8_t* __restrict__ id
     }
 }
 
+// modulation.soft_decoding (modulation.py:29-59): exact log-likelihood ratio of every bit,
+//   llr[i*bps + bps-1-b] = log( sum_{c: bit b of label(c) set} e^{-|y_i-c|^2/nv_i} / sum_{c: bit b clear} e^{...} ),
+// +inf where the denominator underflows to zero (modulation.py:53-54), in double like the reference.
+__global__ void k_soft_llr(const float2* __restrict__ in, const double* __restrict__ nv, size_t nv_n, double* __restrict__ llr,
+                           size_t n_sym, Qam q, double scale, int bps) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_sym) return;
+    const double yr = in[i].x, yi = in[i].y;
+    const double inv_nv = 1.0 / nv[nv_n > 1 ? i : 0];
+    double num[8], den[8];
+#pragma unroll
+    for (int b = 0; b < 8; ++b) num[b] = den[b] = 0.0;
+    const uint32_t n_pts = 1u << bps;
+    for (uint32_t v = 0; v < n_pts; ++v) {
+        const float2 c = qam_symbol(q, v);
+        const double dr = yr - scale * c.x, di = yi - scale * c.y;
+        const double e = exp(-(dr * dr + di * di) * inv_nv);
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            if ((v >> b) & 1u) num[b] += e;
+            else den[b] += e;
+        }
+    }
+    for (int b = 0; b < bps; ++b)
+        llr[i * bps + bps - 1 - b] = den[b] == 0.0 ? (double)INFINITY : log(num[b] / den[b]);
+}
+
 // ---------------------------------------------------------------------------------------------
 // OfdmQamModem.modulate up to the IFFT input (modulation.py:346-382 + :264-267): symbol values of
 // every user -> precode -> sum over users -> place on the n_fft grid, for every antenna.

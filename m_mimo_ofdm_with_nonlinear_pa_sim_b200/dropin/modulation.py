@@ -62,9 +62,8 @@ def demodulate(constellation: ndarray, n_bits_per_symbol: int, input_symbols: nd
 
 
 def soft_decoding(constellation: ndarray, n_bits_per_symbol: int, input_symbols: ndarray, noise_var_vec: ndarray) -> ndarray:
-    """LLR demodulation (modulation.py:29-59).  Only the MATLAB-LDPC scripts use it; those are out of this
-    package's scope and there is deliberately no CPU implementation here."""
-    raise NotImplementedError("soft (LLR) demodulation is outside the CUDA hot path of this package")
+    """Exact LLR demodulation (modulation.py:29-59) on the device: mmimo_qam_soft_llr."""
+    return _abi.get_ops().qam_soft_llr(_desc(constellation), np.atleast_1d(input_symbols), noise_var_vec)
 
 
 # ---- classes --------------------------------------------------------------------------------------

@@ -100,6 +100,23 @@ def detection_margin(symbols: np.ndarray, constel_size: int) -> np.ndarray:
     return np.minimum(axis_margin(z.real), axis_margin(z.imag))
 
 
+def soft_llr(symbols: np.ndarray, constellation: np.ndarray, noise_var) -> np.ndarray:
+    """modulation.soft_decoding, modulation.py:29-59: exact LLR of every bit (MSB of each symbol first),
+    log(sum_{bit set} e^{-|y-c|^2/nv} / sum_{bit clear} e^{...}); +inf where the denominator underflows to zero."""
+    y = np.asarray(symbols, dtype=np.complex128).reshape(-1)
+    nv = np.broadcast_to(np.asarray(noise_var, dtype=np.float64), y.shape)
+    n_bits = int(math.log2(len(constellation)))
+    e = np.exp(-np.abs(y[:, None] - constellation[None, :]) ** 2 / nv[:, None])  # [n, M]
+    labels = np.arange(len(constellation))
+    out = np.empty((y.size, n_bits))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for b in range(n_bits):
+            m = ((labels >> b) & 1).astype(bool)
+            num, den = e[:, m].sum(axis=1), e[:, ~m].sum(axis=1)
+            out[:, n_bits - 1 - b] = np.where(den == 0, np.inf, np.log(num / den))
+    return out.reshape(-1)
+
+
 def calc_alpha(ibo_db):
     """Bussgang shrinking coefficient of the soft limiter.  modulation.py:178-189."""
     gamma = np.power(10.0, np.asarray(ibo_db, dtype=np.float64) / 20.0)
