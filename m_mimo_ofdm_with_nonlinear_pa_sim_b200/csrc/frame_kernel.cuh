@@ -59,7 +59,7 @@ struct FrameArgs {
     // loop_single_user != 0: the loop side models a single-user array instead (main_multiuser_mcnc_ber_vs_ebn0.py:563-572).
     int loop_single_user;
     // multi-point batches (mmimo_link_sweep): frame f counts into err_total[64 * ((frame0 + f) / fpp) + iteration]
-    int fpp; long long frame0;
+    int fpp; unsigned frame0;
 };
 
 constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048;
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 2) k_link_frame(const FrameArgs a
             const unsigned int e = err_s[t];
             err_s[t] = 0;
             if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
-            atomicAdd(&a.err_total[t + (MU ? (f & 1) * 32 : 0) + (a.fpp ? 64 * ((a.frame0 + f) / a.fpp) : 0)], (unsigned long long)e);  // MU: user 1 counts at [32..]
+            atomicAdd(&a.err_total[t + (MU ? (f & 1) * 32 : 0) + (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u)], (unsigned long long)e);  // MU: user 1 counts at [32..]
         }
         __syncthreads();
     }

@@ -123,9 +123,10 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     pa.avg_symbol_power = avg_symbol_power(cfg.constel_size);
     pa.avg_sample_power = pa.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
     pa.snr_lin = pow(10.0, rq->snr_db / 10.0);
-    pa.snr_lin_tab = c->sweep.snr_lin; pa.ibo_lin_tab = c->sweep.ibo_lin; pa.fpp = c->sweep.fpp; pa.frame0 = (long long)c0;
+    SweepArgs sw{c->sweep.snr_lin, c->sweep.ibo_lin, c->sweep.fpp, (unsigned)c0};
     prof_begin(c, PROF_PREP);
-    k_prep_realisation<<<n, 256, 0, c->stream>>>(pa);
+    if (sw.fpp) k_prep_realisation<true><<<n, 256, 0, c->stream>>>(pa, sw);
+    else k_prep_realisation<false><<<n, 256, 0, c->stream>>>(pa, sw);
     prof_end(c);
     c->launches++;
     *h_true_out = h_true;
@@ -251,7 +252,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.corr_out = want_corr ? c->corr.as<float2>() : nullptr;
         fa.err_out = (rs && rs->err_per_frame) ? c->err.as<uint32_t>() : nullptr;
         fa.err_total = c->sweep.fpp ? c->sweep.counters : counters;
-        fa.fpp = c->sweep.fpp; fa.frame0 = (long long)c0;
+        fa.fpp = c->sweep.fpp; fa.frame0 = (unsigned)c0;
         if (c->rxeq_scr.reserve((size_t)8 * c->n_sm * N_SC * 8)) return 1;  // >= the largest grid launch_frame uses
         fa.rxeq_scratch = c->rxeq_scr.as<float2>();
         const int grid = n;

@@ -124,7 +124,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             pa.n_ant = K; pa.n_frames = ni; pa.pa_kind = cfg.pa_kind; pa.is_mcnc = 1;
             pa.ibo_lin = mp.ibo_lin; pa.avg_symbol_power = mp.avg_symbol_power; pa.avg_sample_power = mp.avg_sample_power;
             pa.snr_lin = mp.snr_lin;
-            k_prep_realisation<<<ni, 256, 0, c->stream>>>(pa);
+            k_prep_realisation<false><<<ni, 256, 0, c->stream>>>(pa, SweepArgs{});
             k_copy_loop_p0<<<nblk(ni), 256, 0, c->stream>>>(c->scal.as<FrameScalars>(), c->s_d.as<FrameScalars>(), ni);
             c->launches += 2;
             fa.loop.v = nullptr; fa.loop.v_fs = 0;

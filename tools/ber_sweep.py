@@ -96,10 +96,36 @@ def run_fixed_ber(eng, a, rank=0, world=1, exchange=None):
     return ibos, req, ber, frames
 
 
+def run_nant_chan(eng, a, rank=0, world=1, exchange=None):
+    """BER versus number of antennas versus channel type at one Eb/N0
+    (main_mp_clipping_noise_cancellation/main_mp_miso_mcnc_ber_vs_nant_vs_chan.py:80-150).  CSV layout of that script:
+    row 0 the antenna counts, then per channel (los, two_path, rayleigh) one row per result slot (no distortion,
+    standard receiver, iterations 1..I)."""
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200.parallel import link_batch_runner, monte_carlo_point
+    n_ants = [int(v) for v in a.n_ants.split(",")]
+    chans = a.channels.split(",")
+    ebn0 = axis(a.ebn0)[0]
+    bits_frame = int(math.log2(a.constel)) * 2048
+    snr = 10 * math.log10(10 ** (ebn0 / 10) * math.log2(a.constel))
+    rows = np.zeros((len(chans), a.n_iter + 2, len(n_ants)))
+    frames = 0
+    for ci, ch in enumerate(chans):
+        for ni, n_ant in enumerate(n_ants):
+            eng.configure(constel_size=a.constel, n_ant=n_ant, pa=a.pa, ibo_db=axis(a.ibo)[0], channel=ch, receiver=a.receiver)
+            runner = link_batch_runner(eng, a.n_iter, snr, seed=a.seed + 7919 * (ci * 64 + ni), csi_eps=a.csi_eps, incl_clean_run=True)
+            err, bits, n = monte_carlo_point(runner, a.n_iter + 2, bits_frame, int(a.err_min), int(a.bits_max), a.frames_per_step,
+                                             rank, world, exchange)
+            rows[ci, :, ni] = err / bits
+            frames += n
+    return np.array(n_ants, dtype=float), rows.reshape(-1, len(n_ants)), frames
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--sweep", choices=["ebn0", "ibo", "fixed-ber"], default="ebn0")
+    ap.add_argument("--sweep", choices=["ebn0", "ibo", "fixed-ber", "nant-chan"], default="ebn0")
     ap.add_argument("--target-ber", type=float, default=1e-2)
+    ap.add_argument("--n-ants", default="1,2,4,8,16,32,64,128", help="nant-chan sweep: antenna counts")
+    ap.add_argument("--channels", default="los,two_path,rayleigh", help="nant-chan sweep: channel types")
     ap.add_argument("--ebn0", default="5:20:0.5")
     ap.add_argument("--ibo", default="0")
     ap.add_argument("--n-ant", type=int, default=64)
@@ -129,7 +155,9 @@ def main():
     eng = LinkEngine(local)
     eng.configure(constel_size=a.constel, n_ant=a.n_ant, pa=a.pa, ibo_db=axis(a.ibo)[0], channel=a.channel, receiver=a.receiver)
     t0 = time.time()
-    if a.sweep == "fixed-ber":
+    if a.sweep == "nant-chan":
+        ax, rows, frames = run_nant_chan(eng, a, rank, world, exchange)
+    elif a.sweep == "fixed-ber":
         ax, rows, _ber, frames = run_fixed_ber(eng, a, rank, world, exchange)
     else:
         ax, rows, frames = run_sweep(eng, a, rank, world, exchange)
