@@ -38,14 +38,21 @@ struct ChanArgs {
     int n_usr;
 };
 
-__device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bool skip_att) {
-    const double x = d * f * (1.0 / C_LIGHT);
+// one propagation path: amp / f * exp(+j 2 pi d f / c), amp = gain c / (4 pi d) (channel.py:56-66); the phase (thousands
+// of cycles) is range-reduced in double, the amplitude needs fp32 only.  d_over_c and amp are per (frame, antenna).
+__device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float amp, bool skip_att) {
+    const double x = d_over_c * f;
     const float r = (float)(x - rint(x));
     float s, c;
     sincospif(2.0f * r, &s, &c);
     if (skip_att) return make_float2(c, s);
-    const float a = (float)(gain * C_LIGHT / (4.0 * 3.14159265358979323846 * d * f));
+    const float a = amp / (float)f;
     return make_float2(a * c, a * s);
+}
+
+// the same from distance and linear gain (stage kernels: one realisation per call)
+__device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bool skip_att) {
+    return path_coeff(d * (1.0 / C_LIGHT), f, (float)(gain * C_LIGHT / (4.0 * 3.14159265358979323846 * d)), skip_att);
 }
 
 __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
@@ -79,16 +86,23 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
         d2 = a.tx_pos[k * 3 + 2] / sn + rx[2] / sn;
     }
     float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+    const double amp0 = a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846);
+    const double t1 = d1 * (1.0 / C_LIGHT), t2 = d2 * (1.0 / C_LIGHT);
+    const float amp1 = (float)(amp0 / d1), amp2 = a.kind == 1 ? (float)(amp0 / d2) : 0.f;
+    // two adjacent slots per thread and step: 16-byte stores, 16-byte table loads
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) {
-        const int p = jp * 256 + t;
-        const double fr = a.freq_slot[p];
-        float2 h = path_coeff(d1, fr, a.gain_lin, a.skip_attenuation);
+    for (int j = 0; j < 4; ++j) {
+        const int p = j * 512 + 2 * t;
+        const double2 fr = *reinterpret_cast<const double2*>(a.freq_slot + p);
+        float2 h0 = path_coeff(t1, fr.x, amp1, a.skip_attenuation);
+        float2 h1 = path_coeff(t1, fr.y, amp1, a.skip_attenuation);
         if (a.kind == 1) {
-            const float2 g = path_coeff(d2, fr, a.gain_lin, a.skip_attenuation);
-            h.x -= g.x; h.y -= g.y;
+            const float2 g0 = path_coeff(t2, fr.x, amp2, a.skip_attenuation);
+            const float2 g1 = path_coeff(t2, fr.y, amp2, a.skip_attenuation);
+            h0.x -= g0.x; h0.y -= g0.y;
+            h1.x -= g1.x; h1.y -= g1.y;
         }
-        out[p] = h;
+        *reinterpret_cast<float4*>(out + p) = make_float4(h0.x, h0.y, h1.x, h1.y);
     }
 }
 
