@@ -172,7 +172,9 @@ typedef struct mmimo_mu_request {
     int32_t n_frames;          /* channel realisations; each yields one frame per user */
     int32_t n_iter;
     int32_t precoding;         /* MMIMO_MU_MRT / MMIMO_MU_ZF */
-    int32_t loop_single_user;  /* 0: McncMuReceiver (corrector.py:348); 1: per-user single-user McncReceiver (MRT of its own channel) */
+    int32_t loop_single_user;  /* 0: McncMuReceiver (corrector.py:348); 1: per-user single-user McncReceiver, MRT of its own
+                                  channel (the script with mr_precoding; with zf_precoding the script's single-user arrays
+                                  use the phase-only branch antenna_array.py:175-178 - stage path only) */
     double snr_db;
     uint64_t seed;
     uint64_t frame_id0;

@@ -60,7 +60,10 @@ def test_mu_full_frame_vs_reference(engine, tag):
 
 
 def test_mu_single_user_loop_vs_oracle(engine):
+    """loop_single_user: oracle mu_frame(loop_single_user=True) is pinned bit-exact to the reference run of the script's
+    receivers (tests/golden/mu_su_loop.npz); the GPU path is compared with both"""
     g, cfg, hl, tx_idx, real = mu_case("mrt")
+    gs = load_golden("mu_su_loop")
     ref = lo.mu_frame(cfg, hl, tx_idx, None, 2, "mrt", loop_single_user=True, real=real)
     engine.configure(n_ant=8, channel="injected", pa="softlim", ibo_db=2.0, receiver="mcnc")
     h = np.stack([hl[u][:, cfg.bins] for u in range(2)])[None]
@@ -70,6 +73,8 @@ def test_mu_single_user_loop_vs_oracle(engine):
     for u in range(2):
         assert rel_l2(out["rx_eq"][0, u], ref["rx_eq"][u]) < 2 * TOL
         check_decisions(out["det"][0, u].astype(np.int64), ref["det"][u], cfg)
+        check_decisions(out["det"][0, u].astype(np.int64), gs["det_mrt_u%d" % u].astype(np.int64), cfg)
+        assert np.all(np.abs(out["err"][u].astype(np.int64) - gs["err_mrt_u%d" % u]) <= 12)
 
 
 def test_mu_device_rng_ber(engine):
