@@ -16,6 +16,15 @@ for chan, rx in (("los", "mcnc"), ("rayleigh", "cnc"), ("two_path", "mcnc")):
     out = eng.simulate(3, 2, 20.0, seed=5, incl_clean_run=True, csi_eps=0.1 if chan == "los" else 0.0,
                        dumps=("det", "err_per_frame", "rx_eq", "corr", "h_true", "v", "agc", "pa_p0", "alpha", "clean_det"))
     print(chan, rx, out["err"].tolist(), out["clean_err"].tolist())
+# two-user fused path (both precoders, both receiver loops, all dumps), multi-point batch, SDR snapshots
+eng.configure(n_ant=3, channel="los", receiver="mcnc", ibo_db=1.0)
+for tag in ("mrt", "zf"):
+    for su in (False, True):
+        out = eng.mu_simulate(3, 2, 20.0, precoding=tag, loop_single_user=su, seed=9, dumps=("det", "rx_eq", "v", "agc", "pa_p0"))
+        print("mu", tag, su, out["err"].tolist())
+eng.configure(n_ant=3, channel="two_path", receiver="mcnc", ibo_db=1.0)
+print("sweep", eng.sweep([15.0, 20.0, 25.0], [0.0, 2.0, 4.0], 3, 2, seed=4).tolist())
+print("sdr", [v.tolist() for v in eng.sdr(3, seed=2)])
 eng.close()
 
 dropin.install()
@@ -48,6 +57,7 @@ rcv.update_agc()
 res = rcv.receive([0, 1, 2], y / rcv.agc_corr_vec, other_usr_bits=bits[0])
 cmu = corrector.CncMuReceiver(copy.deepcopy(mod), copy.deepcopy(pa))
 res2 = cmu.receive([0, 2], y, other_usr_symbols=mod.modulate(bits, get_symbols_only=True)[0])
+llr = mod.soft_detection_llr(mod.modulate(bits, get_symbols_only=True)[0] + 0.1, noise_var=0.5)
 td = utilities.to_time_domain(x)
 fd = utilities.to_freq_domain(td, remove_cp=False)
 print("stage ops ok", utilities.count_mismatched_bits(res[0], bits[1]), len(res2), float(np.abs(fd - x).max()))
