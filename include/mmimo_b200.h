@@ -164,17 +164,23 @@ int mmimo_sdr_simulate(mmimo_ctx* ctx, const mmimo_sdr_request* req, double* des
  * per user (MisoLosFd / MisoTwoPathFd / MisoRayleighFd / injected), multi-user MRT or zero-forcing precoding
  * (antenna_array.py:202-257), array PA re-normalisation (:313-360), one array transmission carrying both users
  * (modulation.py:373), per user: propagate over its channel, AWGN, AGC, then McncMuReceiver.receive with knowledge of the
- * other user's bits (corrector.py:404-446) or - loop_single_user - the single-user McncReceiver of the script (:563-572).
+ * other user's bits (corrector.py:404-446) or one of the other receivers of the multi-user scripts (MMIMO_MU_RX_*).
  * Arrays with a user axis are ordered [n_frames][2][...]; err is [2][n_iter+1].  NULL optional inputs = generated on the
  * device (Philox keyed on (seed, 2*frame + user)). */
 enum { MMIMO_MU_MRT = 0, MMIMO_MU_ZF = 1 };
+/* per-user receiver of the two-user loop:
+ *   MCNC_MU  McncMuReceiver (corrector.py:348-489): full two-user array model, other user's bits known
+ *   MCNC_SU  single-user McncReceiver on the user's own channel, MRT (main_multiuser_mcnc_ber_vs_ebn0.py:563-572 with
+ *            mr_precoding; with zf_precoding the script's single-user arrays use the phase-only branch
+ *            antenna_array.py:175-178 - stage path only)
+ *   CNC      single-antenna CncReceiver (corrector.py:12-112; main_multiuser_cnc_ber_vs_ebn0.py:124,600)
+ *   CNC_MU   CncMuReceiver (corrector.py:248-345): single-antenna model fed with sqrt(2)/2 (own + other user's symbols) */
+enum { MMIMO_MU_RX_MCNC_MU = 0, MMIMO_MU_RX_MCNC_SU = 1, MMIMO_MU_RX_CNC = 2, MMIMO_MU_RX_CNC_MU = 3 };
 typedef struct mmimo_mu_request {
     int32_t n_frames;          /* channel realisations; each yields one frame per user */
     int32_t n_iter;
     int32_t precoding;         /* MMIMO_MU_MRT / MMIMO_MU_ZF */
-    int32_t loop_single_user;  /* 0: McncMuReceiver (corrector.py:348); 1: per-user single-user McncReceiver, MRT of its own
-                                  channel (the script with mr_precoding; with zf_precoding the script's single-user arrays
-                                  use the phase-only branch antenna_array.py:175-178 - stage path only) */
+    int32_t receiver;          /* MMIMO_MU_RX_*: which receiver runs per user (below) */
     double snr_db;
     uint64_t seed;
     uint64_t frame_id0;

@@ -39,7 +39,7 @@ class SdrRequest(C.Structure):
 
 
 class MuRequest(C.Structure):
-    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("precoding", C.c_int32), ("loop_single_user", C.c_int32),
+    _fields_ = [("n_frames", C.c_int32), ("n_iter", C.c_int32), ("precoding", C.c_int32), ("receiver", C.c_int32),
                 ("snr_db", C.c_double), ("seed", C.c_uint64), ("frame_id0", C.c_uint64), ("usr_pos", (C.c_double * 3) * 2),
                 ("rx_pos", c_d_p), ("h", c_f_p), ("tx_idx", c_u8_p), ("noise", c_f_p), ("rx_eq_in", c_f_p)]
 

@@ -16,6 +16,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
     if (!c || !rq || !rs || !rs->err) return fail("mmimo_mu_link_simulate: NULL argument (result.err is required)");
     if (!c->configured) return fail("mmimo_mu_link_simulate: context not configured (call mmimo_configure)");
     if (rq->n_iter < 0 || rq->n_iter > 31) return fail("mmimo_mu_link_simulate: n_iter must be 0..31 (got %d)", rq->n_iter);
+    if (rq->receiver < 0 || rq->receiver > MMIMO_MU_RX_CNC_MU) return fail("mmimo_mu_link_simulate: unknown receiver %d", rq->receiver);
     if (rq->precoding != MMIMO_MU_MRT && rq->precoding != MMIMO_MU_ZF) return fail("mmimo_mu_link_simulate: unknown precoding %d", rq->precoding);
     if (rq->frame_id0 >> 62) return fail("mmimo_mu_link_simulate: frame_id0 too large");
     CK(cudaSetDevice(c->device));
@@ -97,6 +98,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
         mp.avg_symbol_power = avg_symbol_power(cfg.constel_size);
         mp.avg_sample_power = mp.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
         mp.snr_lin = pow(10.0, rq->snr_db / 10.0);
+        mp.loop_cnc = rq->receiver == MMIMO_MU_RX_CNC || rq->receiver == MMIMO_MU_RX_CNC_MU;
         k_prep_mu<<<nr, 256, 0, c->stream>>>(mp);
         c->launches++;
 
@@ -109,8 +111,24 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
         fa.tx.agc_inv = c->agc_inv.as<float2>(); fa.tx.agc_fs = N_SC;
         fa.tx.k = K;
         fa.loop = fa.tx;
-        fa.loop_single_user = rq->loop_single_user ? 1 : 0;
-        if (rq->loop_single_user) {
+        fa.loop_single_user = (rq->receiver == MMIMO_MU_RX_MCNC_SU || rq->receiver == MMIMO_MU_RX_CNC) ? 1 : 0;
+        if (mp.loop_cnc) {
+            // single-antenna model of the transmitter (corrector.py:52-112, :288-345): h = 1, estimate / alpha; CncMuReceiver
+            // adds the other user's true symbols with equal power: explicit "precoder" rows sqrt(2)/2 for both users
+            if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 4) || c->cnc_agc_inv.reserve(N_SC * 8) || c->s_a.reserve(N_SC * 8)) return 1;
+            const double alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
+            k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_ones.as<float2>(), make_float2(1.f, 0.f), N_SC);
+            k_fill_f<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float>(), 1.f / 64.f, N_SC);
+            k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_agc_inv.as<float2>(), make_float2((float)(1.0 / (64.0 * alpha)), 0.f), N_SC);
+            k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->s_a.as<float2>(), make_float2(0.70710678118654752440f, 0.f), N_SC);
+            c->launches += 4;
+            fa.loop.h_mac = c->cnc_ones.as<float2>(); fa.loop.h_mac_fs = 0;
+            fa.loop.h_pre = c->cnc_ones.as<float2>(); fa.loop.h_pre_fs = 0;
+            fa.loop.v = rq->receiver == MMIMO_MU_RX_CNC_MU ? c->s_a.as<float2>() : nullptr; fa.loop.v_fs = 0;
+            fa.loop.sscale = c->cnc_v.as<float>(); fa.loop.sscale_fs = 0;
+            fa.loop.agc_inv = c->cnc_agc_inv.as<float2>(); fa.loop.agc_fs = 0;
+            fa.loop.k = 1;
+        } else if (rq->receiver == MMIMO_MU_RX_MCNC_SU) {
             // the script's receivers: McncReceiver over a single-user copy of the array, MRT of the user's own channel
             // (main_multiuser_mcnc_ber_vs_ebn0.py:563-572) -> the single-user realisation kernel per instance
             if (c->s_a.reserve((size_t)ni * N_SC * 4) || c->s_b.reserve((size_t)ni * N_SC * 8) || c->s_c.reserve((size_t)ni * N_SC * 8) ||

@@ -16,6 +16,7 @@ struct MuPrepArgs {
     FrameScalars* scal;     // [R][2]
     float* alpha_out;       // [R][K] or nullptr
     int n_ant, n_real, precoding, pa_kind;
+    int loop_cnc;           // receiver loop = single-antenna CNC model: its PA sees avg_symbol_power * n_sc / n_fft (corrector.py:34-35)
     double ibo_lin, avg_symbol_power, avg_sample_power, snr_lin;
 };
 
@@ -135,6 +136,7 @@ __global__ void __launch_bounds__(256) k_prep_mu(const MuPrepArgs a) {
         const double p0 = (a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / avg : a.ibo_lin * avg;
         FrameScalars sc;
         sc.pa_p0_tx = sc.pa_p0_loop = (float)p0;
+        if (a.loop_cnc) sc.pa_p0_loop = (float)((a.pa_kind == PA_TOI) ? (1.0 / a.ibo_lin) / a.avg_sample_power : a.ibo_lin * a.avg_sample_power);
         sc.noise_sigma_clean = 0.f;
         sc.noise_sigma = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s0 / N_SC) / a.snr_lin));  // noise.py:64-66
         a.scal[2 * r] = sc;

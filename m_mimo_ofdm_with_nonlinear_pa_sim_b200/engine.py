@@ -227,9 +227,11 @@ class LinkEngine:
         return err
 
     def mu_simulate(self, n_frames, n_iter, snr_db, *, precoding="mrt", usr_pos=((212.0, 212.0, 1.5), (150.0, 250.0, 1.5)),
-                    loop_single_user=False, seed=0, frame_id0=0, inject=None, dumps=()):
+                    loop_single_user=False, receiver=None, seed=0, frame_id0=0, inject=None, dumps=()):
         """Fused two-user frames (main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642, corrector.py:348-489):
         n_frames channel realisations, one frame per user each.  precoding "mrt" | "zf" (antenna_array.py:202-257).
+        receiver: "mcnc_mu" (McncMuReceiver, default) | "mcnc_su" (single-user McncReceiver, = loop_single_user=True) |
+        "cnc" (CncReceiver) | "cnc_mu" (CncMuReceiver, corrector.py:248-345).
         inject: optional rx_pos [n,2,3], h [n,2,K,2048], tx_idx [n,2,2048], noise [n,2,2048], rx_eq_in [n,2,2048].
         dumps: any of "det", "rx_eq", "v", "agc", "pa_p0".  Returns dict with err [2, n_iter+1], bits (per user)."""
         if self.cfg is None:
@@ -240,7 +242,8 @@ class LinkEngine:
         rq = _lib.MuRequest()
         rq.n_frames, rq.n_iter, rq.snr_db = n, int(n_iter), float(snr_db)
         rq.precoding = {"mrt": 0, "zf": 1}[precoding]
-        rq.loop_single_user = 1 if loop_single_user else 0
+        receiver = receiver or ("mcnc_su" if loop_single_user else "mcnc_mu")
+        rq.receiver = {"mcnc_mu": 0, "mcnc_su": 1, "cnc": 2, "cnc_mu": 3}[receiver]
         rq.seed, rq.frame_id0 = int(seed) & (2 ** 64 - 1), int(frame_id0)
         for u in range(2):
             for i in range(3):

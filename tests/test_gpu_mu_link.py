@@ -94,3 +94,19 @@ def test_mu_device_rng_ber(engine):
     b0 = engine.mu_simulate(4, 2, snr, precoding="zf", seed=5, frame_id0=0)
     b1 = engine.mu_simulate(4, 2, snr, precoding="zf", seed=5, frame_id0=4)
     assert np.array_equal(a["err"], b0["err"] + b1["err"])
+
+
+@pytest.mark.parametrize("receiver, key", [("cnc", "cnc"), ("cnc_mu", "cncmu")])
+def test_mu_cnc_receivers_vs_reference(engine, receiver, key):
+    """single-antenna receivers of the multi-user scripts on the fused path: CncReceiver and CncMuReceiver
+    (corrector.py:12-112, :248-345); golden from the unmodified reference (tests/golden/mu_su_loop.npz), noise free"""
+    g, cfg, hl, tx_idx, real = mu_case("mrt")
+    gs = load_golden("mu_su_loop")
+    engine.configure(n_ant=8, channel="injected", pa="softlim", ibo_db=2.0, receiver="mcnc")
+    h = np.stack([hl[u][:, cfg.bins] for u in range(2)])[None]
+    out = engine.mu_simulate(1, 2, 300.0, precoding="mrt", receiver=receiver,
+                             inject=dict(h=h, tx_idx=tx_idx[None], noise=np.zeros((1, 2, cfg.n_sub_carr), np.complex64)),
+                             dumps=("det",))
+    for u in range(2):
+        check_decisions(out["det"][0, u].astype(np.int64), gs["%s_det_u%d" % (key, u)].astype(np.int64), cfg)
+        assert np.all(np.abs(out["err"][u].astype(np.int64) - gs["%s_err_u%d" % (key, u)]) <= 12)

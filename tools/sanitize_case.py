@@ -21,6 +21,7 @@ eng.configure(n_ant=3, channel="los", receiver="mcnc", ibo_db=1.0)
 for tag in ("mrt", "zf"):
     for su in (False, True):
         out = eng.mu_simulate(3, 2, 20.0, precoding=tag, loop_single_user=su, seed=9, dumps=("det", "rx_eq", "v", "agc", "pa_p0"))
+        out = eng.mu_simulate(3, 2, 20.0, precoding=tag, receiver="cnc_mu" if su else "cnc", seed=9)
         print("mu", tag, su, out["err"].tolist())
 eng.configure(n_ant=3, channel="two_path", receiver="mcnc", ibo_db=1.0)
 print("sweep", eng.sweep([15.0, 20.0, 25.0], [0.0, 2.0, 4.0], 3, 2, seed=4).tolist())
