@@ -62,7 +62,7 @@ def run_fixed_ber(eng, a, rank=0, world=1, exchange=None):
     n_it = a.n_iter + 1
     ber = np.full((len(ibos), len(ebn0s), n_it), np.nan)
     frames = 0
-    fpp = max(world, (a.frames_per_step // world) * world)  # frames per point and round, split evenly over the ranks
+    fpp = a.frames_per_step   # frames per point and round
     for i, ibo in enumerate(ibos):
         err = np.zeros((len(ebn0s), n_it)); bits = np.zeros((len(ebn0s), n_it))
         rnd = 0
@@ -71,15 +71,16 @@ def run_fixed_ber(eng, a, rank=0, world=1, exchange=None):
             if not active.any():
                 break
             pts = np.nonzero(active.any(axis=1))[0]
-            lo, cnt = shard_range(fpp, rank, world)
-            # every rank runs its share of each point's frames; ids are unique per (ibo, round, point, frame)
-            fid0 = ((i * 4096 + rnd) * len(ebn0s)) * fpp
+            # the active points of this round form ONE batch with frame ids base + j * fpp + frame (j = position in `pts`);
+            # every rank runs a contiguous block of points of that batch, so the counters do not depend on the rank count
+            j0, cnt = shard_range(len(pts), rank, world)
+            base = ((i * 4096 + rnd) * len(ebn0s)) * fpp
             e = np.zeros((len(pts), n_it))
             if cnt > 0:
-                e = eng.sweep(snr[pts], np.full(len(pts), ibo), cnt, a.n_iter, seed=a.seed, frame_id0=fid0 + lo * len(pts),
-                              csi_eps=a.csi_eps).astype(np.float64)
+                e[j0:j0 + cnt] = eng.sweep(snr[pts[j0:j0 + cnt]], np.full(cnt, ibo), fpp, a.n_iter, seed=a.seed,
+                                           frame_id0=base + j0 * fpp, csi_eps=a.csi_eps)
             if exchange is not None:
-                e = exchange.allreduce(e.ravel()).reshape(len(pts), n_it)
+                e = exchange.allreduce(e.ravel()).reshape(len(pts), n_it).astype(np.float64)
             for j, p in enumerate(pts):
                 err[p] += np.where(active[p], e[j], 0)
                 bits[p] += np.where(active[p], fpp * bits_frame, 0)
