@@ -28,7 +28,7 @@ def test_round_trip_without_pa_is_error_free(engine, channel):
     engine.configure(n_ant=64, channel=channel, pa="softlim", ibo_db=40.0, receiver="mcnc")
     out = engine.simulate(512, 3, 60.0, seed=17, incl_clean_run=True)
     assert out["err"].tolist() == [0, 0, 0, 0] and int(out["clean_err"][0]) == 0
-    assert int(out["bits"][0]) == 512 * 12288
+    assert int(np.ravel(out["bits"])[0]) == 512 * 12288
 
 
 def test_counters_do_not_depend_on_sharding_or_batching(engine):
@@ -55,7 +55,7 @@ def test_extreme_configurations(engine):
     for constel in (4, 16, 256):
         engine.configure(constel_size=constel, n_ant=64, channel="los", pa="rapp", ibo_db=3.0, receiver="cnc")
         out = engine.simulate(16, 2, 40.0, seed=4)
-        assert np.all(out["err"] <= out["bits"]) and int(out["bits"][0]) == 16 * 2048 * int(np.log2(constel))
+        assert np.all(out["err"] <= out["bits"]) and int(np.ravel(out["bits"])[0]) == 16 * 2048 * int(np.log2(constel))
     engine.configure(n_ant=1, channel="los", pa="softlim", ibo_db=0.0, receiver="cnc")
     out = engine.simulate(64, 5, snr_of(25.0), seed=5)
     assert out["err"][5] < out["err"][0]
