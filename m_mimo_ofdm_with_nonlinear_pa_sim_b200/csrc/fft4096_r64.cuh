@@ -184,4 +184,35 @@ __device__ __forceinline__ void fft4096_r64(pf2 (&x)[64], pf2* __restrict__ buf,
     radix64<S, false, PRUNE_OUT>(x);
 }
 
+// Variant with the loads software-pipelined by hand: the inter-pass twiddles are fetched DEPTH elements ahead of
+// the multiply that uses them, and the exchange is read back in the order stage A of the second pass consumes
+// it (q, q+16, q+32, q+48), so the first butterflies start after four loads instead of forty-nine.
+// `after_exchange` runs once the group has finished reading the exchange buffer (the buffer is free from there
+// until the next transform's stores), before the second radix-64 pass.
+template <int S, bool PRUNE_IN, bool PRUNE_OUT, int DEPTH = 8, class SYNC = SyncGroup, class HOOK = NoHook>
+__device__ __forceinline__ void fft4096_r64_pipelined(pf2 (&x)[64], pf2* __restrict__ buf, const TwSmem64& tw,
+                                                      const int lane, const SYNC sy,
+                                                      const HOOK after_exchange = HOOK()) {
+    radix64<S, PRUNE_IN, false>(x);
+    float2 w[DEPTH];
+#pragma unroll
+    for (int p = 0; p < DEPTH; ++p) w[p] = tw.t[rev64(p) * 64 + lane];
+#pragma unroll
+    for (int p = 0; p < 64; ++p) {
+        const int k0 = rev64(p);
+        const float2 wp = w[p % DEPTH];
+        if (p + DEPTH < 64) w[p % DEPTH] = tw.t[rev64(p + DEPTH) * 64 + lane];
+        const pf2 v = k0 == 0 ? x[p] : (S > 0) ? pcmulc(x[p], wp.x, wp.y) : pcmul(x[p], wp.x, wp.y);
+        buf[k0 * 64 + (lane ^ k0)] = v;
+    }
+    sy.x_sync();
+#pragma unroll
+    for (int q = 0; q < 16; ++q)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) x[q + 16 * m] = buf[lane * 64 + ((q + 16 * m) ^ lane)];
+    sy.x_sync();
+    after_exchange();
+    radix64<S, false, PRUNE_OUT>(x);
+}
+
 }  // namespace mmimo

@@ -1,0 +1,259 @@
+// Fused Monte-Carlo frame kernel, two-pass radix-64 form: same frame semantics as k_link_frame (frame_kernel.cuh;
+// mp_model.py:208-222 with corrector.py:165-207 / :52-112 inlined), different work decomposition:
+//   * one CTA of 256 threads per SM, split into four 64-thread groups; each group runs WHOLE antenna chains
+//     (precode -> IFFT -> PA -> FFT -> MAC) with 64 points per thread and ONE shared-memory exchange per transform
+//     (fft4096_r64.cuh), the four groups take antennas g, g+4, g+8, ... of the same frame and pass;
+//   * the group's 32 KB exchange buffer is idle from the end of the FFT exchange to the start of the next IFFT
+//     exchange; in that window one thread streams the channel row of this antenna (for the MAC) and the precoder
+//     / channel-knowledge row of the group's next antenna into it with cp.async.bulk (TMA, mbarrier completion), so
+//     no global-memory latency is exposed to the two warps of the group;
+//   * every group keeps the partial sum over ITS antennas in registers; the four partial sums are added through
+//     the (idle) exchange buffers at the end of the pass, always in the same order (results do not depend on how
+//     the groups are scheduled);
+//   * the pass epilogue (AWGN, AGC, slicing, distortion estimate, error counting) runs on the native slot layout
+//     p = jp*256 + t exactly as in k_link_frame.
+// Thread (group g, lane n0) owns slots lane + 64 i, i = 0..31 <-> transform register n1 = i (i < 16) or i + 32
+// <-> bin lane + 64 n1; slot 0 carries bin 1024 (register 16 of lane 0), bin 0 is unused (link_common.cuh).
+#pragma once
+#include "fft4096_r64.cuh"
+#include "frame_kernel.cuh"
+
+namespace mmimo {
+
+constexpr int R64_GROUPS = 4;
+constexpr int FRAME64_SMEM_BYTES = (4096 + R64_GROUPS * 4096 + N_SC) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+constexpr unsigned ROW_BYTES = N_SC * 8;
+#ifndef R64_TW_DEPTH
+#define R64_TW_DEPTH 4
+#endif
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned mb, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mb), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned mb, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_parity(unsigned mb, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_TX:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@!p bra WAIT_TX;\n"
+        "}\n" ::"r"(mb), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared, completion counted in bytes on `mb`
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned mb) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mb) : "memory");
+}
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
+template <int PA>
+__global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameArgs a, const float2* __restrict__ tw4096) {
+    extern __shared__ __align__(128) float2 smem[];
+    float2* tw = smem;                                          // W4096^(n0 k0) at [k0*64 + n0]
+    pf2* bufs = reinterpret_cast<pf2*>(smem + 4096);            // [group][4096]
+    float2* symn_s = smem + 4096 + R64_GROUPS * 4096;           // scaled current symbols, native slots
+    unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC);
+    unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
+    float2* rxeq_s = a.rxeq_scratch + (size_t)blockIdx.x * N_SC;  // per-CTA scratch, stays in L2
+
+    const int t = threadIdx.x, lane = t & 63, g = t >> 6;
+    pf2* buf = bufs + g * 4096;
+    const float2* rowA = reinterpret_cast<const float2*>(buf);   // channel row of the antenna being accumulated
+    const float2* rowB = rowA + N_SC;                            // precoder / CSI row of the group's next antenna
+    const unsigned mbA = smem_u32(mbar_s + 2 * g), mbB = mbA + 8;  // completion of the rowA / rowB copies
+    const SyncGroup sy{g + 1};
+    const TwSmem64 tws{tw};
+    for (int i = t; i < 4096; i += FFT_THREADS) tw[i] = tw4096[((i >> 6) * (i & 63)) & 4095];
+    if (t < 64) err_s[t] = 0;
+    if (t < 2 * R64_GROUPS) mbar_init(smem_u32(mbar_s + t), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    unsigned phA = 0, phB = 0;  // parities of the mbarrier phases to wait for next
+
+    for (int f = blockIdx.x; f < a.n_frames; f += gridDim.x) {
+        const FrameScalars sc = a.scal[f * a.scal_fs];
+        uint32_t txw[2];
+        if (a.tx_idx) {
+            const uint8_t* p = a.tx_idx + (size_t)f * N_SC;
+            txw[0] = txw[1] = 0;
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
+        } else {
+            uint32_t r[4];
+            const uint64_t fid = a.frame_id0 + f;
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
+                          (uint32_t)(a.seed >> 32), r);
+            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+            txw[0] = r[0] & m4;
+            txw[1] = r[1] & m4;
+        }
+        uint32_t curw[2] = {txw[0], txw[1]};
+
+        for (int pass = 0; pass <= a.n_iter; ++pass) {
+            const bool first = (pass == 0);
+            const TxSide& sd = first ? a.tx : a.loop;
+            const int K = (first && a.rx_eq_in) ? 0 : sd.k;
+            const float2* __restrict__ Hm = sd.h_mac + f * sd.h_mac_fs;
+            const float2* __restrict__ Hp = sd.v ? sd.v + f * sd.v_fs : sd.h_pre + f * sd.h_pre_fs;
+            const bool explicit_v = sd.v != nullptr;
+            const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
+            const float sqrt_p0 = sqrtf(p0);
+            {
+                const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) {
+                    const int p = jp * 256 + t;
+                    const float2 s = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float gsc = ss[p];
+                    symn_s[p] = make_float2(s.x * gsc, s.y * gsc);
+                }
+            }
+            __syncthreads();  // symbols visible to all groups; every exchange buffer is idle from here
+
+            if (g < K) {  // precoder row of the group's first antenna
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_expect_tx(mbB, ROW_BYTES);
+                    bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
+                    bulk_prefetch_l2(Hm + (size_t)g * N_SC, ROW_BYTES);
+                    if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
+                }
+            }
+            pf2 acc[32];  // partial sum over this group's antennas
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] = pk(0.f, 0.f);
+            for (int k = g; k < K; k += R64_GROUPS) {
+                pf2 x[64];
+                mbar_wait_parity(mbB, phB);
+                phB ^= 1u;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int n1 = i < 16 ? i : i + 32;
+                    const float2 s = symn_s[lane + 64 * i];
+                    const pf2 h = pk2(rowB[lane + 64 * i]);
+                    if (explicit_v) x[n1] = pcmul(h, s.x, s.y);
+                    else x[n1] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));  // conj(h) * s
+                }
+#pragma unroll
+                for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
+                if (lane == 0) { x[16] = x[0]; x[0] = pk(0.f, 0.f); }
+                sy.x_sync();  // rows fully consumed by the whole group before the exchange overwrites them
+                fft4096_r64_pipelined<+1, true, false, R64_TW_DEPTH>(x, buf, tws, lane, sy);
+                pf2 y[64];
+#pragma unroll
+                for (int n1 = 0; n1 < 64; ++n1) y[n1] = pa_apply_pk<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1);
+                fft4096_r64_pipelined<-1, false, true, R64_TW_DEPTH>(y, buf, tws, lane, sy, [&]() {
+                    if (lane == 0) {
+                        const bool more = k + R64_GROUPS < K;
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_expect_tx(mbA, ROW_BYTES);
+                        bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
+                        if (more) {
+                            mbar_expect_tx(mbB, ROW_BYTES);
+                            bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
+                            if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
+                            if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                        }
+                    }
+                });
+                mbar_wait_parity(mbA, phA);
+                phA ^= 1u;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int n1 = i < 16 ? i : i + 32;
+                    pf2 yv = y[rev64(n1)];
+                    if (i == 0 && lane == 0) yv = y[rev64(16)];
+                    acc[i] = pcfma(yv, pk2(rowA[lane + 64 * i]), acc[i]);
+                }
+            }
+            // ---- the four groups' partial sums meet in the (idle) exchange buffers: fixed summation order ----
+            sy.x_sync();  // the group's last MAC has read its channel row
+#pragma unroll
+            for (int i = 0; i < 32; ++i) buf[lane + 64 * i] = acc[i];
+            __syncthreads();
+            pf2 accn[8];
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const int p = jp * 256 + t;
+                accn[jp] = padd(padd(bufs[p], bufs[4096 + p]), padd(bufs[2 * 4096 + p], bufs[3 * 4096 + p]));
+            }
+
+            // ---- end of pass: equalise / estimate distortion / slice / count (as k_link_frame) -----------
+            uint32_t detw[2] = {0u, 0u};
+            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
+            float2 nz[8];
+            if (first && !a.rx_eq_in) {
+                if (a.noise) {
+                    const float ns = a.noise_unit ? sc.noise_sigma : 1.0f;
+#pragma unroll
+                    for (int jp = 0; jp < 8; ++jp) {
+                        const float2 u = a.noise[(size_t)f * N_SC + jp * 256 + t];
+                        nz[jp] = make_float2(u.x * ns, u.y * ns);
+                    }
+                } else {
+                    const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        uint32_t r[4];
+                        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_NOISE, (uint32_t)(t * 4 + q),
+                                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+                        const float2 g0 = box_muller(r[0], r[1]), g1 = box_muller(r[2], r[3]);
+                        nz[2 * q] = make_float2(g0.x * sc.noise_sigma, g0.y * sc.noise_sigma);
+                        nz[2 * q + 1] = make_float2(g1.x * sc.noise_sigma, g1.y * sc.noise_sigma);
+                    }
+                }
+            }
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const int p = jp * 256 + t;
+                const float2 ac = unpk(accn[jp]);
+                float2 corr;
+                if (first) {
+                    if (a.rx_eq_in) {
+                        corr = a.rx_eq_in[(size_t)f * N_SC + p];
+                    } else {
+                        const float2 r = make_float2(fmaf(64.f, nz[jp].x, ac.x), fmaf(64.f, nz[jp].y, ac.y));
+                        corr = cmul(r, ai[p]);
+                    }
+                    rxeq_s[p] = corr;
+                    if (a.rx_eq_out) a.rx_eq_out[(size_t)f * N_SC + p] = corr;
+                } else {
+                    const float2 z = cmul(ac, ai[p]);
+                    const float2 sy0 = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float2 d = csub(z, sy0);   // distortion estimate, corrector.py:205
+                    corr = csub(rxeq_s[p], d);       // corrector.py:184
+                }
+                if (a.corr_out) a.corr_out[((size_t)f * (a.n_iter + 1) + pass) * N_SC + p] = corr;
+                const uint32_t idx = qam_detect(a.qam, corr);
+                detw[jp >> 2] |= idx << (8 * (jp & 3));
+            }
+            curw[0] = detw[0];
+            curw[1] = detw[1];
+            unsigned int nerr = __popc(detw[0] ^ txw[0]) + __popc(detw[1] ^ txw[1]);
+            nerr = __reduce_add_sync(0xffffffffu, nerr);
+            if ((t & 31) == 0) atomicAdd(&err_s[pass], nerr);
+            if (a.det_out) {
+                uint8_t* dp = a.det_out + ((size_t)f * (a.n_iter + 1) + pass) * N_SC;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) dp[jp * 256 + t] = (uint8_t)((detw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+            }
+        }
+        __syncthreads();
+        if (t <= a.n_iter) {
+            const unsigned int e = err_s[t];
+            err_s[t] = 0;
+            if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
+            atomicAdd(&a.err_total[t + (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u)], (unsigned long long)e);
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace mmimo

@@ -14,6 +14,7 @@
 #include "../../include/mmimo_b200.h"
 #include "prep_kernels.cuh"
 #include "mu_kernels.cuh"
+#include "frame_kernel_r64.cuh"
 #include "stage_kernels.cuh"
 
 using namespace mmimo;
@@ -177,6 +178,10 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     CK(cudaFuncSetAttribute(k_link_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_r64<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_r64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_r64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_r64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
     if (stage_kernels_init()) { delete c; return 1; }
     *out = c;
     return 0;

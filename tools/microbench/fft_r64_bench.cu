@@ -88,6 +88,12 @@ __global__ void __launch_bounds__(NT, 1) k(float2* out, const float2* twg, int i
 #pragma unroll
             for (int n1 = 0; n1 < 64; ++n1) y[n1] = pa_apply_pk<PA_SOFT_LIMITER>(x[rev64(n1)], 1.0f, 1.0f, 0.f);
             if (TWR) fft4096_r64<-1, false, true>(y, buf, twr, lane, SyncGroup{g + 1}); else fft4096_r64<-1, false, true>(y, buf, tws, lane, SyncGroup{g + 1});
+        } else if (MODE == 3 || MODE == 4) {
+            constexpr int D = MODE == 3 ? 8 : 16;
+            fft4096_r64_pipelined<+1, true, false, D>(x, buf, tws, lane, SyncGroup{g + 1});
+#pragma unroll
+            for (int n1 = 0; n1 < 64; ++n1) y[n1] = pa_apply_pk<PA_SOFT_LIMITER>(x[rev64(n1)], 1.0f, 1.0f, 0.f);
+            fft4096_r64_pipelined<-1, false, true, D>(y, buf, tws, lane, SyncGroup{g + 1});
         } else if (MODE == 1) {
             if (TWR) fft4096_r64<+1, true, false>(x, buf, twr, lane, SyncNone64()); else fft4096_r64<+1, true, false>(x, buf, tws, lane, SyncNone64());
 #pragma unroll
@@ -220,6 +226,8 @@ int main(int argc, char** argv) {
     run<0>("r64 full chain (IFFT, PA, FFT)", d, dtw, nsm);
     run<1>("r64 butterflies + twiddle loads only", d, dtw, nsm);
     run<2>("r64 full chain, no barriers", d, dtw, nsm);
+    run<3>("r64 chain, pipelined loads (8)", d, dtw, nsm);
+    run<4>("r64 chain, pipelined loads (16)", d, dtw, nsm);
     run<0, true>("r64 full chain, register twiddles", d, dtw, nsm);
     run<0, false, 384>("r64 full chain, 6 groups/SM", d, dtw, nsm);
     run<0, false, 320>("r64 full chain, 5 groups/SM", d, dtw, nsm);
