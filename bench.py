@@ -310,7 +310,8 @@ def run_gpu(a):
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                          "traffic_note": "dram__bytes_read+write per launch from profiles/frame_kernel_traffic.json (ncu --set full, "
                                          "1184-frame launch) scaled to this launch's frame count; algorithmic HBM bytes per launch = %d" % (bytes_frame * F),
-                         "kernel": "k_link_frame<soft limiter>", "launches_timed": frame_n,
+                         "kernel": ("k_link_frame<soft limiter>" if os.environ.get("MMIMO_FRAME_KERNEL", "").startswith("r1")
+                                    else "k_link_frame_r64<soft limiter>"), "launches_timed": frame_n,
                          "kernel_ms_per_launch": frame_ms / max(frame_n, 1),
                          "kernel_share_of_step": frame_ms / ms_total if ms_total else None,
                          "algorithmic_flops_per_frame": fl,

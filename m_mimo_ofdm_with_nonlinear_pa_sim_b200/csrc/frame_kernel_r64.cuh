@@ -21,10 +21,15 @@
 namespace mmimo {
 
 constexpr int R64_GROUPS = 4;
-constexpr int FRAME64_SMEM_BYTES = (4096 + R64_GROUPS * 4096 + N_SC) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+#ifndef R64_ACC_SMEM
+#define R64_ACC_SMEM 16  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
+#endif
+constexpr int FRAME64_SMEM_BYTES =
+    (4096 + R64_GROUPS * 4096 + N_SC + R64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+static_assert(FRAME64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
 constexpr unsigned ROW_BYTES = N_SC * 8;
 #ifndef R64_TW_DEPTH
-#define R64_TW_DEPTH 4
+#define R64_TW_DEPTH 16
 #endif
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -58,11 +63,12 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
     float2* tw = smem;                                          // W4096^(n0 k0) at [k0*64 + n0]
     pf2* bufs = reinterpret_cast<pf2*>(smem + 4096);            // [group][4096]
     float2* symn_s = smem + 4096 + R64_GROUPS * 4096;           // scaled current symbols, native slots
-    unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC);
+    unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC + R64_ACC_SMEM * FFT_THREADS);
     unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
     float2* rxeq_s = a.rxeq_scratch + (size_t)blockIdx.x * N_SC;  // per-CTA scratch, stays in L2
 
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
+    pf2* accx_s = reinterpret_cast<pf2*>(symn_s + N_SC) + t;    // accumulators i < R64_ACC_SMEM at [i * 256]
     pf2* buf = bufs + g * 4096;
     const float2* rowA = reinterpret_cast<const float2*>(buf);   // channel row of the antenna being accumulated
     const float2* rowB = rowA + N_SC;                            // precoder / CSI row of the group's next antenna
@@ -126,9 +132,12 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
                     if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
                 }
             }
-            pf2 acc[32];  // partial sum over this group's antennas
+            pf2 acc[32];  // partial sum over this group's antennas (entries < R64_ACC_SMEM unused: in accx_s)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) acc[i] = pk(0.f, 0.f);
+            for (int i = 0; i < 32; ++i) {
+                acc[i] = pk(0.f, 0.f);
+                if (i < R64_ACC_SMEM) accx_s[i * FFT_THREADS] = pk(0.f, 0.f);
+            }
             for (int k = g; k < K; k += R64_GROUPS) {
                 pf2 x[64];
                 mbar_wait_parity(mbB, phB);
@@ -138,45 +147,72 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
                     const int n1 = i < 16 ? i : i + 32;
                     const float2 s = symn_s[lane + 64 * i];
                     const pf2 h = pk2(rowB[lane + 64 * i]);
-                    if (explicit_v) x[n1] = pcmul(h, s.x, s.y);
-                    else x[n1] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));  // conj(h) * s
+                    // the CONJUGATE of the precoded sample (see the transform loop below)
+                    if (explicit_v) x[n1] = pcmulc(pmul(h, pk(1.f, -1.f)), s.x, s.y);  // conj(v) * conj(s)
+                    else x[n1] = pcmulc(h, s.x, s.y);                                  // conj(conj(h) * s) = h * conj(s)
                 }
 #pragma unroll
                 for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
                 if (lane == 0) { x[16] = x[0]; x[0] = pk(0.f, 0.f); }
                 sy.x_sync();  // rows fully consumed by the whole group before the exchange overwrites them
-                fft4096_r64_pipelined<+1, true, false, R64_TW_DEPTH>(x, buf, tws, lane, sy);
-                pf2 y[64];
+                // ONE forward-transform body serves both directions (the unrolled code of two specialised
+                // transforms is ~80 KB and the groups' instruction fetches then thrash the instruction cache):
+                //   IFFT(x) = conj(FFT(conj x)),  PA(conj u) = conj(PA(u))  (every PA model is a real gain),
+                //   FFT(PA(IFFT(x))) = FFT(conj(PA(u))),  u = FFT(conj x).
+                // The digit reversal between the two transforms is folded into the destination registers of the PA.
+#pragma unroll 1
+                for (int half = 0; half < 2; ++half) {
+                    fft4096_r64_pipelined<-1, false, false, R64_TW_DEPTH>(x, buf, tws, lane, sy, [&]() {
+                        if (half == 1 && lane == 0) {
+                            const bool more = k + R64_GROUPS < K;
+                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                            mbar_expect_tx(mbA, ROW_BYTES);
+                            bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
+                            if (more) {
+                                mbar_expect_tx(mbB, ROW_BYTES);
+                                bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
+                                if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
+                                if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                            }
+                        }
+                    });
+                    if (half == 0) {
 #pragma unroll
-                for (int n1 = 0; n1 < 64; ++n1) y[n1] = pa_apply_pk<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1);
-                fft4096_r64_pipelined<-1, false, true, R64_TW_DEPTH>(y, buf, tws, lane, sy, [&]() {
-                    if (lane == 0) {
-                        const bool more = k + R64_GROUPS < K;
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        mbar_expect_tx(mbA, ROW_BYTES);
-                        bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
-                        if (more) {
-                            mbar_expect_tx(mbB, ROW_BYTES);
-                            bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
-                            if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
-                            if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                        for (int n1 = 0; n1 < 64; ++n1) {
+                            if (n1 <= rev64(n1)) {
+                                const pf2 u0 = pmul(pa_apply_pk<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1), pk(1.f, -1.f));
+                                const pf2 u1 = pmul(pa_apply_pk<PA>(x[n1], p0, sqrt_p0, a.pa_p1), pk(1.f, -1.f));
+                                x[n1] = u0;
+                                x[rev64(n1)] = u1;
+                            }
                         }
                     }
-                });
+                }
+                pf2 (&y)[64] = x;
                 mbar_wait_parity(mbA, phA);
                 phA ^= 1u;
+                {   // all loads before the first store: the compiler cannot prove rowA / accx_s disjoint
+                    pf2 hv[32], av[R64_ACC_SMEM > 0 ? R64_ACC_SMEM : 1];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const int n1 = i < 16 ? i : i + 32;
-                    pf2 yv = y[rev64(n1)];
-                    if (i == 0 && lane == 0) yv = y[rev64(16)];
-                    acc[i] = pcfma(yv, pk2(rowA[lane + 64 * i]), acc[i]);
+                    for (int i = 0; i < 32; ++i) hv[i] = pk2(rowA[lane + 64 * i]);
+#pragma unroll
+                    for (int i = 0; i < R64_ACC_SMEM; ++i) av[i] = accx_s[i * FFT_THREADS];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int n1 = i < 16 ? i : i + 32;
+                        pf2 yv = y[rev64(n1)];
+                        if (i == 0 && lane == 0) yv = y[rev64(16)];
+                        if (i < R64_ACC_SMEM) av[i] = pcfma(yv, hv[i], av[i]);
+                        else acc[i] = pcfma(yv, hv[i], acc[i]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < R64_ACC_SMEM; ++i) accx_s[i * FFT_THREADS] = av[i];
                 }
             }
             // ---- the four groups' partial sums meet in the (idle) exchange buffers: fixed summation order ----
             sy.x_sync();  // the group's last MAC has read its channel row
 #pragma unroll
-            for (int i = 0; i < 32; ++i) buf[lane + 64 * i] = acc[i];
+            for (int i = 0; i < 32; ++i) buf[lane + 64 * i] = i < R64_ACC_SMEM ? accx_s[i * FFT_THREADS] : acc[i];
             __syncthreads();
             pf2 accn[8];
 #pragma unroll

@@ -7,10 +7,10 @@ static double calc_alpha_host(double ibo_db) {  // modulation.py:178-189
 
 template <int PA>
 static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int n) {
-    // MMIMO_FRAME_KERNEL=r64 selects the two-pass radix-64 decomposition (frame_kernel_r64.cuh): same results to
-    // rounding, measured 4 % slower than the default three-pass radix-16 kernel (profiles/r01_r64_frame_kernel.txt)
+    // Default: the two-pass radix-64 kernel (frame_kernel_r64.cuh).  MMIMO_FRAME_KERNEL=r16 selects the three-pass
+    // radix-16 kernel (measurement knob; same results to rounding, measured 4 % slower on the headline case).
     const char* fk = getenv("MMIMO_FRAME_KERNEL");
-    if (fk && fk[0] == 'r' && fk[1] == '6') {
+    if (!(fk && fk[0] == 'r' && fk[1] == '1')) {
         k_link_frame_r64<PA><<<std::min(n, c->n_sm), FFT_THREADS, FRAME64_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>());
         return;
     }

@@ -12,6 +12,7 @@
 #include "../../m_mimo_ofdm_with_nonlinear_pa_sim_b200/csrc/fft4096_r64.cuh"
 using namespace mmimo;
 
+__device__ __forceinline__ pf2 pconj(pf2 a) { return pmul(a, pk(1.f, -1.f)); }
 struct SyncNone64 {
     static constexpr bool kExchange = false;
     __device__ __forceinline__ void x_sync() const {}
@@ -94,6 +95,27 @@ __global__ void __launch_bounds__(NT, 1) k(float2* out, const float2* twg, int i
 #pragma unroll
             for (int n1 = 0; n1 < 64; ++n1) y[n1] = pa_apply_pk<PA_SOFT_LIMITER>(x[rev64(n1)], 1.0f, 1.0f, 0.f);
             fft4096_r64_pipelined<-1, false, true, D>(y, buf, tws, lane, SyncGroup{g + 1});
+        } else if (MODE == 5 || MODE == 6) {
+            // ONE transform body for both directions: IFFT(x) = conj(FFT(conj x)), the limiter commutes with conj,
+            // no pruning; the digit-reversal between the transforms is folded into the limiter's destination registers
+            constexpr int D = MODE == 5 ? 8 : 4;
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                fft4096_r64_pipelined<-1, false, false, D>(x, buf, tws, lane, SyncGroup{g + 1});
+                if (half == 0) {
+#pragma unroll
+                    for (int n1 = 0; n1 < 64; ++n1) {
+                        if (n1 <= rev64(n1)) {
+                            const pf2 a = pconj(pa_apply_pk<PA_SOFT_LIMITER>(x[rev64(n1)], 1.0f, 1.0f, 0.f));
+                            const pf2 b = pconj(pa_apply_pk<PA_SOFT_LIMITER>(x[n1], 1.0f, 1.0f, 0.f));
+                            x[n1] = a;
+                            x[rev64(n1)] = b;
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int n1 = 0; n1 < 64; ++n1) y[n1] = x[n1];
         } else if (MODE == 1) {
             if (TWR) fft4096_r64<+1, true, false>(x, buf, twr, lane, SyncNone64()); else fft4096_r64<+1, true, false>(x, buf, tws, lane, SyncNone64());
 #pragma unroll
@@ -228,6 +250,12 @@ int main(int argc, char** argv) {
     run<2>("r64 full chain, no barriers", d, dtw, nsm);
     run<3>("r64 chain, pipelined loads (8)", d, dtw, nsm);
     run<4>("r64 chain, pipelined loads (16)", d, dtw, nsm);
+    run<3>("r64 chain, pipelined (8), groups 2,3 late", d, dtw, nsm, 3500);
+    run<3>("r64 chain, pipelined (8), groups 2,3 late", d, dtw, nsm, 7000);
+    run<4>("r64 chain, pipelined (16), groups 2,3 late", d, dtw, nsm, 7000);
+    run<5>("r64 one shared transform body (8)", d, dtw, nsm);
+    run<6>("r64 one shared transform body (4)", d, dtw, nsm);
+    run<5>("r64 shared body (8), groups 2,3 late", d, dtw, nsm, 3500);
     run<0, true>("r64 full chain, register twiddles", d, dtw, nsm);
     run<0, false, 384>("r64 full chain, 6 groups/SM", d, dtw, nsm);
     run<0, false, 320>("r64 full chain, 5 groups/SM", d, dtw, nsm);
