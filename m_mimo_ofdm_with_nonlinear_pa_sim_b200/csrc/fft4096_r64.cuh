@@ -61,8 +61,8 @@ __device__ __forceinline__ void bf4(pf2& a0, pf2& a1, pf2& a2, pf2& a3) {
 // In-register 64-point DFT (sign S), natural order in, digit-reversed out: X[k] ends up in x[rev64(k)].
 //   PRUNE_IN : x[17..47] are known to be zero (values ignored); x[16] is honoured (the stray bin, see below)
 //   PRUNE_OUT: only k in 0..16 and 48..63 are produced
-template <int S, bool PRUNE_IN, bool PRUNE_OUT>
-__device__ __forceinline__ void radix64(pf2 (&x)[64]) {
+template <int S, bool PRUNE_IN>
+__device__ __forceinline__ void radix64_stage_a(pf2 (&x)[64]) {
     // stage A: butterflies over m (stride 16), then W64^(q r)
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
@@ -84,6 +84,23 @@ __device__ __forceinline__ void radix64(pf2 (&x)[64]) {
             bf4<S>(x[q], x[q + 16], x[q + 32], x[q + 48]);
         }
     }
+}
+template <int S, bool PRUNE_OUT>
+__device__ __forceinline__ void radix64_stage_c(pf2 (&x)[64]) {
+    // stage C: sixteen radix-4 butterflies on adjacent quadruples; output r'' is the HIGH digit of k
+#pragma unroll
+    for (int b = 0; b < 16; ++b) {
+        if (PRUNE_OUT && b != 0) {  // only r'' = 0 and 3 (k < 16 or k >= 48); block 0 also yields k = 16
+            const pf2 a0 = x[4 * b], a1 = x[4 * b + 1], a2 = x[4 * b + 2], a3 = x[4 * b + 3];
+            x[4 * b] = padd(padd(a0, a2), padd(a1, a3));
+            x[4 * b + 3] = paddj<-S>(psub(a0, a2), psub(a1, a3));
+        } else {
+            bf4<S>(x[4 * b], x[4 * b + 1], x[4 * b + 2], x[4 * b + 3]);
+        }
+    }
+}
+template <int S>
+__device__ __forceinline__ void radix64_stage_b(pf2 (&x)[64]) {
 #define MMIMO_TWA(q)                                   \
     x[q + 16] = pmulw64<S, (q) * 1>(x[q + 16]);        \
     x[q + 32] = pmulw64<S, (q) * 2>(x[q + 32]);        \
@@ -106,17 +123,20 @@ __device__ __forceinline__ void radix64(pf2 (&x)[64]) {
         x[16 * r + 2 + 12] = pmulw64<S, 24>(x[16 * r + 2 + 12]);
         x[16 * r + 3 + 12] = pmulw64<S, 36>(x[16 * r + 3 + 12]);
     }
-    // stage C: sixteen radix-4 butterflies on adjacent quadruples; output r'' is the HIGH digit of k
-#pragma unroll
-    for (int b = 0; b < 16; ++b) {
-        if (PRUNE_OUT && b != 0) {  // only r'' = 0 and 3 (k < 16 or k >= 48); block 0 also yields k = 16
-            const pf2 a0 = x[4 * b], a1 = x[4 * b + 1], a2 = x[4 * b + 2], a3 = x[4 * b + 3];
-            x[4 * b] = padd(padd(a0, a2), padd(a1, a3));
-            x[4 * b + 3] = paddj<-S>(psub(a0, a2), psub(a1, a3));
-        } else {
-            bf4<S>(x[4 * b], x[4 * b + 1], x[4 * b + 2], x[4 * b + 3]);
-        }
-    }
+}
+template <int S, bool PRUNE_IN, bool PRUNE_OUT>
+__device__ __forceinline__ void radix64(pf2 (&x)[64]) {
+    radix64_stage_a<S, PRUNE_IN>(x);
+    radix64_stage_b<S>(x);
+    radix64_stage_c<S, PRUNE_OUT>(x);
+}
+// same with the pruning decided at run time (uniform branches around the two small pruned stages): lets ONE
+// unrolled transform body serve a pruned-input and a pruned-output transform
+template <int S>
+__device__ __forceinline__ void radix64_rt(pf2 (&x)[64], const bool prune_in, const bool prune_out) {
+    if (prune_in) radix64_stage_a<S, true>(x); else radix64_stage_a<S, false>(x);
+    radix64_stage_b<S>(x);
+    if (prune_out) radix64_stage_c<S, true>(x); else radix64_stage_c<S, false>(x);
 }
 
 // Named barrier of one 64-thread group (ids 1..15; 0 is __syncthreads)
@@ -213,6 +233,36 @@ __device__ __forceinline__ void fft4096_r64_pipelined(pf2 (&x)[64], pf2* __restr
     sy.x_sync();
     after_exchange();
     radix64<S, false, PRUNE_OUT>(x);
+}
+
+// Run-time pruned form of fft4096_r64_pipelined (see radix64_rt): the first pass prunes its input when
+// prune_in, the second pass prunes its output when prune_out.
+// `after_exchange` runs once the group has finished reading the exchange buffer (the buffer is free from there
+// until the next transform's stores), before the second radix-64 pass.
+template <int S, int DEPTH = 8, class SYNC = SyncGroup, class HOOK = NoHook>
+__device__ __forceinline__ void fft4096_r64_pipelined_rt(pf2 (&x)[64], pf2* __restrict__ buf, const TwSmem64& tw,
+                                                         const int lane, const SYNC sy, const bool prune_in,
+                                                         const bool prune_out, const HOOK after_exchange = HOOK()) {
+    radix64_rt<S>(x, prune_in, false);
+    float2 w[DEPTH];
+#pragma unroll
+    for (int p = 0; p < DEPTH; ++p) w[p] = tw.t[rev64(p) * 64 + lane];
+#pragma unroll
+    for (int p = 0; p < 64; ++p) {
+        const int k0 = rev64(p);
+        const float2 wp = w[p % DEPTH];
+        if (p + DEPTH < 64) w[p % DEPTH] = tw.t[rev64(p + DEPTH) * 64 + lane];
+        const pf2 v = k0 == 0 ? x[p] : (S > 0) ? pcmulc(x[p], wp.x, wp.y) : pcmul(x[p], wp.x, wp.y);
+        buf[k0 * 64 + (lane ^ k0)] = v;
+    }
+    sy.x_sync();
+#pragma unroll
+    for (int q = 0; q < 16; ++q)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) x[q + 16 * m] = buf[lane * 64 + ((q + 16 * m) ^ lane)];
+    sy.x_sync();
+    after_exchange();
+    radix64_rt<S>(x, false, prune_out);
 }
 
 }  // namespace mmimo

@@ -22,14 +22,14 @@ namespace mmimo {
 
 constexpr int R64_GROUPS = 4;
 #ifndef R64_ACC_SMEM
-#define R64_ACC_SMEM 16  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
+#define R64_ACC_SMEM 12  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
 #endif
 constexpr int FRAME64_SMEM_BYTES =
     (4096 + R64_GROUPS * 4096 + N_SC + R64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
 static_assert(FRAME64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
 constexpr unsigned ROW_BYTES = N_SC * 8;
 #ifndef R64_TW_DEPTH
-#define R64_TW_DEPTH 16
+#define R64_TW_DEPTH 32
 #endif
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -155,7 +155,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
                 for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
                 if (lane == 0) { x[16] = x[0]; x[0] = pk(0.f, 0.f); }
                 sy.x_sync();  // rows fully consumed by the whole group before the exchange overwrites them
-                // ONE forward-transform body serves both directions (the unrolled code of two specialised
+                // ONE forward-transform body serves both directions (no input / output pruning: deciding it at run
+                // time with uniform branches around the pruned stages measured 1.6 % SLOWER, the basic-block
+                // boundaries cost more scheduling freedom than the 4 % fewer butterfly operations return)
+                // - (the unrolled code of two specialised
                 // transforms is ~80 KB and the groups' instruction fetches then thrash the instruction cache):
                 //   IFFT(x) = conj(FFT(conj x)),  PA(conj u) = conj(PA(u))  (every PA model is a real gain),
                 //   FFT(PA(IFFT(x))) = FFT(conj(PA(u))),  u = FFT(conj x).
