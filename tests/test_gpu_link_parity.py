@@ -200,3 +200,24 @@ def test_multi_point_sweep_equals_point_by_point(engine):
     e2 = engine.sweep(snr[:2], None, fpp, n_iter, seed=5)
     r0 = engine.simulate(fpp, n_iter, float(snr[0]), seed=5, frame_id0=0)["err"]
     assert np.array_equal(e2[0], r0)
+
+
+def test_radix64_and_radix16_frame_kernels_agree(engine, monkeypatch):
+    """The default frame kernel (two-pass radix-64, frame_kernel_r64.cuh) and the three-pass radix-16 kernel
+    (frame_kernel.cuh, MMIMO_FRAME_KERNEL=r16) are two decompositions of the same frame: equalised samples agree to
+    fp32 rounding, detections differ only on decision boundaries, and each kernel is bit-reproducible run to run (the
+    four antenna groups of the radix-64 kernel are summed in a fixed order)."""
+    for pa, n_ant, rx in (("softlim", 16, "mcnc"), ("rapp", 6, "mcnc"), ("softlim", 8, "cnc"), ("toi", 4, "mcnc")):
+        engine.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=1.0, receiver=rx)
+        outs = {}
+        for kern in ("r64", "r16"):
+            monkeypatch.setenv("MMIMO_FRAME_KERNEL", kern)
+            outs[kern] = engine.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
+            again = engine.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
+            assert np.array_equal(outs[kern]["err"], again["err"]) and np.array_equal(outs[kern]["rx_eq"], again["rx_eq"])
+        monkeypatch.delenv("MMIMO_FRAME_KERNEL")
+        a, b = outs["r64"], outs["r16"]
+        rel = np.linalg.norm(a["rx_eq"] - b["rx_eq"]) / np.linalg.norm(b["rx_eq"])
+        assert rel < 2e-6, (pa, rel)
+        assert (a["det"] != b["det"]).mean() < 1e-3, pa
+        assert np.abs(a["err"].astype(np.int64) - b["err"].astype(np.int64)).max() <= 6, (a["err"], b["err"])
