@@ -207,7 +207,9 @@ def test_radix64_and_radix16_frame_kernels_agree(engine, monkeypatch):
     (frame_kernel.cuh, MMIMO_FRAME_KERNEL=r16) are two decompositions of the same frame: equalised samples agree to
     fp32 rounding, detections differ only on decision boundaries, and each kernel is bit-reproducible run to run (the
     four antenna groups of the radix-64 kernel are summed in a fixed order)."""
-    for pa, n_ant, rx in (("softlim", 16, "mcnc"), ("rapp", 6, "mcnc"), ("softlim", 8, "cnc"), ("toi", 4, "mcnc")):
+    # antenna counts that leave groups of the radix-64 kernel idle or ragged (1, 5, 6) included
+    for pa, n_ant, rx in (("softlim", 16, "mcnc"), ("rapp", 6, "mcnc"), ("softlim", 8, "cnc"), ("toi", 4, "mcnc"),
+                          ("softlim", 1, "mcnc"), ("softlim", 5, "cnc"), ("none", 3, "mcnc")):
         engine.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=1.0, receiver=rx)
         outs = {}
         for kern in ("r64", "r16"):
