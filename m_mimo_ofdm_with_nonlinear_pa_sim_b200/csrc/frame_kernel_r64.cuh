@@ -29,7 +29,7 @@ constexpr int FRAME64_SMEM_BYTES =
 static_assert(FRAME64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
 constexpr unsigned ROW_BYTES = N_SC * 8;
 #ifndef R64_TW_DEPTH
-#define R64_TW_DEPTH 32
+#define R64_TW_DEPTH 20
 #endif
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
