@@ -25,7 +25,7 @@ constexpr int R64_GROUPS = 4;
 #define R64_ACC_SMEM 12  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
 #endif
 constexpr int FRAME64_SMEM_BYTES =
-    (4096 + R64_GROUPS * 4096 + N_SC + R64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+    (4096 + R64_GROUPS * 4096 + 2 * N_SC + R64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
 static_assert(FRAME64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
 constexpr unsigned ROW_BYTES = N_SC * 8;
 #ifndef R64_TW_DEPTH
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
     float2* symn_s = smem + 4096 + R64_GROUPS * 4096;           // scaled current symbols, native slots
     unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC + R64_ACC_SMEM * FFT_THREADS);
     unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
-    float2* rxeq_s = a.rxeq_scratch + (size_t)blockIdx.x * N_SC;  // per-CTA scratch, stays in L2
+    float2* rxeq_s = reinterpret_cast<float2*>(mbar_s + 2 * R64_GROUPS);  // equalised received signal of the frame
 
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
     pf2* accx_s = reinterpret_cast<pf2*>(symn_s + N_SC) + t;    // accumulators i < R64_ACC_SMEM at [i * 256]
@@ -122,6 +122,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_r64(const FrameAr
                 }
             }
             __syncthreads();  // symbols visible to all groups; every exchange buffer is idle from here
+            // what the pass epilogue reads from global memory: on its way to L2 while the antennas are processed
+            if (t < 128) prefetch_l2(sd.agc_inv + f * sd.agc_fs + t * 16);
 
             if (g < K) {  // precoder row of the group's first antenna
                 if (lane == 0) {
