@@ -339,7 +339,10 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames", type=int, default=4096, help="frames per step per GPU")
+    # 4144 = 28 x 148: the frame kernel is persistent with one CTA per SM and one frame per CTA at a time, so a batch
+    # that is a multiple of the SM count has no partially filled last wave (4096 would idle a third of the SMs for
+    # 1/28 of the launch)
+    ap.add_argument("--frames", type=int, default=4144, help="frames per step per GPU")
     ap.add_argument("--n-ant", type=int, default=64)
     ap.add_argument("--n-iter", type=int, default=5)
     ap.add_argument("--ebn0", type=float, default=15.0)
