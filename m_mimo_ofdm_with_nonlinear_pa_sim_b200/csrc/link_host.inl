@@ -78,7 +78,7 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ca.pos_stream = in.pos_stream;
         ca.h_out = h_true; ca.n_ant = K;
         prof_begin(c, PROF_CHAN);
-        k_gen_channel<<<dim3(K, n), 256, 0, c->stream>>>(ca);
+        k_gen_channel<<<dim3((K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), 256, 0, c->stream>>>(ca);
         prof_end(c);
         c->launches++;
     } else if (cfg.channel_kind == MMIMO_CHAN_RAYLEIGH) {

@@ -73,7 +73,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             ca.pos_stream = RNG_POS;
             ca.h_out = h; ca.n_ant = K;
             ca.rx0_tab = usr_tab; ca.n_usr = 2;
-            k_gen_channel<<<dim3(K, ni), 256, 0, c->stream>>>(ca);
+            k_gen_channel<<<dim3((K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, ni), 256, 0, c->stream>>>(ca);
             c->launches++;
         } else if (cfg.channel_kind == MMIMO_CHAN_RAYLEIGH) {
             RayleighArgs ra{};

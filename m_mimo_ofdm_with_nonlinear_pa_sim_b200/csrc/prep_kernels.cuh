@@ -55,54 +55,72 @@ __device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bo
     return path_coeff(d * (1.0 / C_LIGHT), f, (float)(gain * C_LIGHT / (4.0 * 3.14159265358979323846 * d)), skip_att);
 }
 
+constexpr int CHAN_ANT_PER_CTA = 8;  // antennas per CTA: the receiver draw and the geometry set-up are shared
+
+// grid (ceil(K / CHAN_ANT_PER_CTA), F): one CTA writes the rows of up to 8 antennas of one realisation
 __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
-    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
-    double rx[3];
-    if (a.rx_pos_in) {
-        rx[0] = a.rx_pos_in[f * 3 + 0]; rx[1] = a.rx_pos_in[f * 3 + 1]; rx[2] = a.rx_pos_in[f * 3 + 2];
-    } else {
-        uint32_t r[4];
-        const uint64_t fid = a.frame_id0 + f;
-        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.pos_stream, 0u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
-        if (a.rx0_tab) {
-            const double* n0 = a.rx0_tab + (size_t)((a.frame_id0 + f) % (uint64_t)a.n_usr) * 3;
-            rx[0] = n0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
-            rx[1] = n0[1] + (u01(r[2], r[3]) - 0.5) * a.loc_var;
-            rx[2] = n0[2];
+    __shared__ double t1_s[CHAN_ANT_PER_CTA], t2_s[CHAN_ANT_PER_CTA];
+    __shared__ float amp1_s[CHAN_ANT_PER_CTA], amp2_s[CHAN_ANT_PER_CTA];
+    const int kb = blockIdx.x * CHAN_ANT_PER_CTA, f = blockIdx.y, t = threadIdx.x;
+    if (t < CHAN_ANT_PER_CTA && kb + t < a.n_ant) {  // geometry of antenna kb + t (channel.py:56-66, :118-140)
+        const int k = kb + t;
+        double rx[3];
+        if (a.rx_pos_in) {
+            rx[0] = a.rx_pos_in[f * 3 + 0]; rx[1] = a.rx_pos_in[f * 3 + 1]; rx[2] = a.rx_pos_in[f * 3 + 2];
         } else {
-            rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
-            rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
-            rx[2] = a.rx0[2];
+            uint32_t r[4];
+            const uint64_t fid = a.frame_id0 + f;
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.pos_stream, 0u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+            if (a.rx0_tab) {
+                const double* n0 = a.rx0_tab + (size_t)((a.frame_id0 + f) % (uint64_t)a.n_usr) * 3;
+                rx[0] = n0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+                rx[1] = n0[1] + (u01(r[2], r[3]) - 0.5) * a.loc_var;
+                rx[2] = n0[2];
+            } else {
+                rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+                rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
+                rx[2] = a.rx0[2];
+            }
         }
-    }
-    if (a.rx_pos_out && k == 0 && t < 3) a.rx_pos_out[f * 3 + t] = rx[t];
-    const double dx = a.tx_pos[k * 3 + 0] - rx[0], dy = a.tx_pos[k * 3 + 1] - rx[1], dz = a.tx_pos[k * 3 + 2] - rx[2];
-    const double d1 = sqrt(dx * dx + dy * dy + dz * dz);
-    double d2 = 0.0;
-    if (a.kind == 1) {
-        const double dxy = sqrt(dx * dx + dy * dy);
-        const double el = atan((a.tx_pos[k * 3 + 2] + rx[2]) / dxy);
-        const double sn = sin(el);
-        d2 = a.tx_pos[k * 3 + 2] / sn + rx[2] / sn;
-    }
-    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
-    const double amp0 = a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846);
-    const double t1 = d1 * (1.0 / C_LIGHT), t2 = d2 * (1.0 / C_LIGHT);
-    const float amp1 = (float)(amp0 / d1), amp2 = a.kind == 1 ? (float)(amp0 / d2) : 0.f;
-    // two adjacent slots per thread and step: 16-byte stores, 16-byte table loads
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int p = j * 512 + 2 * t;
-        const double2 fr = *reinterpret_cast<const double2*>(a.freq_slot + p);
-        float2 h0 = path_coeff(t1, fr.x, amp1, a.skip_attenuation);
-        float2 h1 = path_coeff(t1, fr.y, amp1, a.skip_attenuation);
+        if (a.rx_pos_out && k == 0) { a.rx_pos_out[f * 3 + 0] = rx[0]; a.rx_pos_out[f * 3 + 1] = rx[1]; a.rx_pos_out[f * 3 + 2] = rx[2]; }
+        const double dx = a.tx_pos[k * 3 + 0] - rx[0], dy = a.tx_pos[k * 3 + 1] - rx[1], dz = a.tx_pos[k * 3 + 2] - rx[2];
+        const double d1 = sqrt(dx * dx + dy * dy + dz * dz);
+        double d2 = 0.0;
         if (a.kind == 1) {
-            const float2 g0 = path_coeff(t2, fr.x, amp2, a.skip_attenuation);
-            const float2 g1 = path_coeff(t2, fr.y, amp2, a.skip_attenuation);
-            h0.x -= g0.x; h0.y -= g0.y;
-            h1.x -= g1.x; h1.y -= g1.y;
+            const double dxy = sqrt(dx * dx + dy * dy);
+            const double el = atan((a.tx_pos[k * 3 + 2] + rx[2]) / dxy);
+            const double sn = sin(el);
+            d2 = a.tx_pos[k * 3 + 2] / sn + rx[2] / sn;
         }
-        *reinterpret_cast<float4*>(out + p) = make_float4(h0.x, h0.y, h1.x, h1.y);
+        const double amp0 = a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846);
+        t1_s[t] = d1 * (1.0 / C_LIGHT);
+        t2_s[t] = d2 * (1.0 / C_LIGHT);
+        amp1_s[t] = (float)(amp0 / d1);
+        amp2_s[t] = a.kind == 1 ? (float)(amp0 / d2) : 0.f;
+    }
+    __syncthreads();
+    // two adjacent slots per thread and step: 16-byte stores, 16-byte table loads (the table stays in registers)
+    double2 fr[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) fr[j] = *reinterpret_cast<const double2*>(a.freq_slot + j * 512 + 2 * t);
+    const int nk = min(CHAN_ANT_PER_CTA, a.n_ant - kb);
+    for (int i = 0; i < nk; ++i) {
+        float2* out = a.h_out + ((size_t)f * a.n_ant + kb + i) * N_SC;
+        const double t1 = t1_s[i], t2 = t2_s[i];
+        const float amp1 = amp1_s[i], amp2 = amp2_s[i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int p = j * 512 + 2 * t;
+            float2 h0 = path_coeff(t1, fr[j].x, amp1, a.skip_attenuation);
+            float2 h1 = path_coeff(t1, fr[j].y, amp1, a.skip_attenuation);
+            if (a.kind == 1) {
+                const float2 g0 = path_coeff(t2, fr[j].x, amp2, a.skip_attenuation);
+                const float2 g1 = path_coeff(t2, fr[j].y, amp2, a.skip_attenuation);
+                h0.x -= g0.x; h0.y -= g0.y;
+                h1.x -= g1.x; h1.y -= g1.y;
+            }
+            *reinterpret_cast<float4*>(out + p) = make_float4(h0.x, h0.y, h1.x, h1.y);
+        }
     }
 }
 
