@@ -36,6 +36,9 @@ struct ChanArgs {
     // position is rx0_tab[user]; here x and y are offset around their OWN nominal values (no cord_y quirk)
     const double* rx0_tab;    // [n_usr][3] or nullptr
     int n_usr;
+    // fused first pass of k_prep_realisation (MRT, precoder derived from this very channel): with grid.x == 1 the CTA
+    // sees all K rows of the realisation and also writes the symbol scale 1 / (64 ||h[:, s]||) (antenna_array.py:170-171)
+    float* sscale_out;        // [F][2048] or nullptr
 };
 
 // one propagation path: amp / f * exp(+j 2 pi d f / c), amp = gain c / (4 pi d) (channel.py:56-66); the phase (thousands
@@ -57,12 +60,14 @@ __device__ __forceinline__ float2 path_coeff(double d, double f, double gain, bo
 
 constexpr int CHAN_ANT_PER_CTA = 8;  // antennas per CTA: the receiver draw and the geometry set-up are shared
 
-// grid (ceil(K / CHAN_ANT_PER_CTA), F): one CTA writes the rows of up to 8 antennas of one realisation
+// grid (ceil(K / CHAN_ANT_PER_CTA), F): one CTA writes the rows of up to 8 antennas of one realisation;
+// grid (1, F) with sscale_out: one CTA writes all K rows and the MRT symbol scale
 __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
-    __shared__ double t1_s[CHAN_ANT_PER_CTA], t2_s[CHAN_ANT_PER_CTA];
-    __shared__ float amp1_s[CHAN_ANT_PER_CTA], amp2_s[CHAN_ANT_PER_CTA];
-    const int kb = blockIdx.x * CHAN_ANT_PER_CTA, f = blockIdx.y, t = threadIdx.x;
-    if (t < CHAN_ANT_PER_CTA && kb + t < a.n_ant) {  // geometry of antenna kb + t (channel.py:56-66, :118-140)
+    __shared__ double t1_s[MAX_ANT], t2_s[MAX_ANT];
+    __shared__ float amp1_s[MAX_ANT], amp2_s[MAX_ANT];
+    const int per_cta = a.sscale_out ? a.n_ant : CHAN_ANT_PER_CTA;
+    const int kb = blockIdx.x * per_cta, f = blockIdx.y, t = threadIdx.x;
+    if (t < per_cta && kb + t < a.n_ant) {  // geometry of antenna kb + t (channel.py:56-66, :118-140)
         const int k = kb + t;
         double rx[3];
         if (a.rx_pos_in) {
@@ -103,7 +108,10 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
     double2 fr[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) fr[j] = *reinterpret_cast<const double2*>(a.freq_slot + j * 512 + 2 * t);
-    const int nk = min(CHAN_ANT_PER_CTA, a.n_ant - kb);
+    const int nk = min(per_cta, a.n_ant - kb);
+    float nrm[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) nrm[j] = 0.f;
     for (int i = 0; i < nk; ++i) {
         float2* out = a.h_out + ((size_t)f * a.n_ant + kb + i) * N_SC;
         const double t1 = t1_s[i], t2 = t2_s[i];
@@ -120,6 +128,17 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
                 h1.x -= g1.x; h1.y -= g1.y;
             }
             *reinterpret_cast<float4*>(out + p) = make_float4(h0.x, h0.y, h1.x, h1.y);
+            // same operation order as the first pass of k_prep_realisation: bit-identical scale
+            nrm[2 * j] = fmaf(h0.x, h0.x, fmaf(h0.y, h0.y, nrm[2 * j]));
+            nrm[2 * j + 1] = fmaf(h1.x, h1.x, fmaf(h1.y, h1.y, nrm[2 * j + 1]));
+        }
+    }
+    if (a.sscale_out) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int p = j * 512 + 2 * t;
+            *reinterpret_cast<float2*>(a.sscale_out + (size_t)f * N_SC + p) =
+                make_float2((1.0f / sqrtf(nrm[2 * j])) * 0.015625f, (1.0f / sqrtf(nrm[2 * j + 1])) * 0.015625f);
         }
     }
 }
@@ -151,6 +170,7 @@ struct PrepArgs {
 struct SweepArgs {
     const double* snr_lin_tab; const double* ibo_lin_tab;
     int fpp; unsigned frame0;   // 32-bit: a 64-bit division is an out-of-line call
+    int sscale_ready;           // the channel kernel has written sscale already: skip the norm pass over H
 };
 
 __device__ __forceinline__ double block_sum_256(double v, double* red_s, int t) {
@@ -177,7 +197,10 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
     float2* Vout = a.v_out ? a.v_out + (size_t)f * K * N_SC : nullptr;
 
     float ninv[8];
-    if (!Vin) {
+    if (!Vin && sw.sscale_ready) {
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) ninv[jp] = a.sscale[(size_t)f * N_SC + jp * 256 + t] * 64.0f;  // exact
+    } else if (!Vin) {
         float nrm[8];
 #pragma unroll
         for (int jp = 0; jp < 8; ++jp) nrm[jp] = 0.f;
