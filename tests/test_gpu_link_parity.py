@@ -223,3 +223,18 @@ def test_radix64_and_radix16_frame_kernels_agree(engine, monkeypatch):
         assert rel < 2e-6, (pa, rel)
         assert (a["det"] != b["det"]).mean() < 1e-3, pa
         assert np.abs(a["err"].astype(np.int64) - b["err"].astype(np.int64)).max() <= 6, (a["err"], b["err"])
+
+
+def test_fused_norm_pass_is_bit_identical(engine):
+    """From 2 realisations per SM on, k_gen_channel writes the MRT symbol scale itself (one CTA per realisation) and
+    k_prep_realisation skips its norm pass; below that the realisation kernel computes it.  Same operation order, so a
+    large batch and the same frames run as small batches give exactly the same counters and samples."""
+    engine.configure(n_ant=16, channel="los", pa="softlim", ibo_db=0.0, receiver="mcnc")
+    n, n_iter = 320, 2                      # 320 >= 2 * 148: fused path
+    big = engine.simulate(n, n_iter, 16.0, seed=9, frame_id0=500, dumps=("rx_eq",))
+    err = np.zeros_like(big["err"])
+    for c0 in range(0, n, 80):              # 80 < 2 * 148: norm pass in the realisation kernel
+        part = engine.simulate(80, n_iter, 16.0, seed=9, frame_id0=500 + c0, dumps=("rx_eq",))
+        err += part["err"]
+        assert np.array_equal(part["rx_eq"], big["rx_eq"][c0:c0 + 80])
+    assert np.array_equal(err, big["err"])
