@@ -1,0 +1,272 @@
+// Fused Monte-Carlo frame kernel, scaled-tangent radix-64 form: the frame semantics and the work decomposition of
+// k_link_frame_r64 (frame_kernel_r64.cuh; mp_model.py:208-222 with corrector.py:165-207 / :52-112 inlined) on the
+// transform of fft4096_t64.cuh, which needs 907 instead of 1208 packed FMA-pipe instructions per transform.
+//   * Both transforms of an antenna chain are FORWARD transforms and nothing is conjugated:
+//       IFFT(x)[n] = FFT(x)[-n] / N, so with the precoded symbols written MIRRORED (bin b at input position -b mod N)
+//       the first transform yields the time signal in natural order, the PA acts on it sample by sample and the
+//       second transform returns the spectrum in natural bin order: FFT(PA(FFT(mirror(x)))) = FFT(PA(N IFFT(x))).
+//     The mirror is free: the scaled symbols and the precoder row are read from shared memory at the mirrored slot
+//     (lane -> 64 - lane, register i -> 31 - i; lane 0 keeps its own column), conflict-free.
+//   * One CTA of 256 threads per SM, four 64-thread groups, each group runs WHOLE antenna chains
+//     (precode -> FFT -> PA -> FFT -> MAC) with 64 points per thread and ONE shared-memory exchange per transform;
+//     channel rows arrive by cp.async.bulk (TMA, mbarrier completion) in the group's idle exchange buffer; the partial
+//     sums of the four groups meet in the exchange buffers in a fixed order (bit-reproducible results).
+// Thread (group g, lane n0) owns slots lane + 64 i, i = 0..31 <-> transform register n1 = i (i < 16) or i + 32
+// <-> bin lane + 64 n1; slot 0 carries bin 1024 (register 16 of lane 0), bin 0 is unused (link_common.cuh).
+#pragma once
+#include "fft4096_t64.cuh"
+#include "frame_kernel_r64.cuh"
+
+namespace mmimo {
+
+#ifndef T64_DEPTH
+#define T64_DEPTH 4  // level-C table entries fetched this many butterfly classes ahead of their use
+#endif
+#ifndef T64_ACC_SMEM
+#define T64_ACC_SMEM 12  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
+#endif
+constexpr int FRAME_T64_SMEM_BYTES =
+    (4096 + R64_GROUPS * 4096 + 2 * N_SC + T64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+static_assert(FRAME_T64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
+
+template <int PA>
+__global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameArgs a, const float2* __restrict__ tab_g) {
+    extern __shared__ __align__(128) float2 smem[];
+    float2* tab = smem;                                         // per-lane twiddle parameters (t64::build_table)
+    pf2* bufs = reinterpret_cast<pf2*>(smem + 4096);            // [group][4096]
+    float2* symn_s = smem + 4096 + R64_GROUPS * 4096;           // scaled current symbols, native slots
+    unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC + T64_ACC_SMEM * FFT_THREADS);
+    unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
+    float2* rxeq_s = reinterpret_cast<float2*>(mbar_s + 2 * R64_GROUPS);  // equalised received signal of the frame
+
+    const int t = threadIdx.x, lane = t & 63, g = t >> 6;
+    pf2* accx_s = reinterpret_cast<pf2*>(symn_s + N_SC) + t;    // accumulators i < T64_ACC_SMEM at [i * 256]
+    pf2* buf = bufs + g * 4096;
+    const float2* rowA = reinterpret_cast<const float2*>(buf);   // channel row of the antenna being accumulated
+    const float2* rowB = rowA + N_SC;                            // precoder / CSI row of the group's next antenna
+    const unsigned mbA = smem_u32(mbar_s + 2 * g), mbB = mbA + 8;  // completion of the rowA / rowB copies
+    const SyncGroup sy{g + 1};
+    for (int i = t; i < t64::TAB_FLOAT2; i += FFT_THREADS) tab[i] = tab_g[i];
+    if (t < 64) err_s[t] = 0;
+    if (t < 2 * R64_GROUPS) mbar_init(smem_u32(mbar_s + t), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    unsigned phA = 0, phB = 0;  // parities of the mbarrier phases to wait for next
+    const t64::TabA tab_a = t64::load_tab_a(tab, lane);
+    // mirrored source slot of register i: (64 - lane) + 64 (31 - i); lane 0 keeps its column, where slot 0 holds
+    // bin 1024: register 16 (i = 0, moved below) <- bin 3072 = slot 1024, register 48 (i = 16) <- bin 1024 = slot 0
+    const int mir = 64 - lane;
+    const int mir0 = lane == 0 ? 1024 : mir + 64 * 31;
+    const int mir16 = lane == 0 ? 0 : mir + 64 * 15;
+
+    for (int f = blockIdx.x; f < a.n_frames; f += gridDim.x) {
+        const FrameScalars sc = a.scal[f * a.scal_fs];
+        uint32_t txw[2];
+        if (a.tx_idx) {
+            const uint8_t* p = a.tx_idx + (size_t)f * N_SC;
+            txw[0] = txw[1] = 0;
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
+        } else {
+            uint32_t r[4];
+            const uint64_t fid = a.frame_id0 + f;
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
+                          (uint32_t)(a.seed >> 32), r);
+            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+            txw[0] = r[0] & m4;
+            txw[1] = r[1] & m4;
+        }
+        uint32_t curw[2] = {txw[0], txw[1]};
+
+        for (int pass = 0; pass <= a.n_iter; ++pass) {
+            const bool first = (pass == 0);
+            const TxSide& sd = first ? a.tx : a.loop;
+            const int K = (first && a.rx_eq_in) ? 0 : sd.k;
+            const float2* __restrict__ Hm = sd.h_mac + f * sd.h_mac_fs;
+            const float2* __restrict__ Hp = sd.v ? sd.v + f * sd.v_fs : sd.h_pre + f * sd.h_pre_fs;
+            const bool explicit_v = sd.v != nullptr;
+            const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
+            const float sqrt_p0 = sqrtf(p0);
+            {
+                const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) {
+                    const int p = jp * 256 + t;
+                    const float2 s = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float gsc = ss[p];
+                    symn_s[p] = make_float2(s.x * gsc, s.y * gsc);
+                }
+            }
+            __syncthreads();  // symbols visible to all groups; every exchange buffer is idle from here
+            // what the pass epilogue reads from global memory: on its way to L2 while the antennas are processed
+            if (t < 128) prefetch_l2(sd.agc_inv + f * sd.agc_fs + t * 16);
+
+            if (g < K) {  // precoder row of the group's first antenna
+                if (lane == 0) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_expect_tx(mbB, ROW_BYTES);
+                    bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
+                    bulk_prefetch_l2(Hm + (size_t)g * N_SC, ROW_BYTES);
+                    if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
+                }
+            }
+            pf2 acc[32];  // partial sum over this group's antennas (entries < T64_ACC_SMEM unused: in accx_s)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                acc[i] = pk(0.f, 0.f);
+                if (i < T64_ACC_SMEM) accx_s[i * FFT_THREADS] = pk(0.f, 0.f);
+            }
+            for (int k = g; k < K; k += R64_GROUPS) {
+                pf2 x[64];
+                mbar_wait_parity(mbB, phB);
+                phB ^= 1u;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int n1 = i < 16 ? i : i + 32;
+                    const int src = i == 0 ? mir0 : i == 16 ? mir16 : mir + 64 * (31 - i);
+                    const float2 s = symn_s[src];
+                    const pf2 h = pk2(rowB[src]);
+                    if (explicit_v) x[n1] = pcmul(h, s.x, s.y);                                 // v * s
+                    else x[n1] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));               // conj(h) * s
+                }
+#pragma unroll
+                for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
+                if (lane == 0) { x[16] = x[0]; x[0] = pk(0.f, 0.f); }
+                sy.x_sync();  // rows fully consumed by the whole group before the exchange overwrites them
+                // ONE transform body serves both transforms of the chain (two specialised, pruned bodies do not fit
+                // the instruction cache next to each other, profiles/r01_r64_frame_kernel.txt); the digit reversal
+                // between them is folded into the destination registers of the PA.
+#pragma unroll 1
+                for (int half = 0; half < 2; ++half) {
+                    fft4096_t64<T64_DEPTH>(x, buf, tab, tab_a, lane, sy, [&]() {
+                        if (half == 1 && lane == 0) {
+                            const bool more = k + R64_GROUPS < K;
+                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                            mbar_expect_tx(mbA, ROW_BYTES);
+                            bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
+                            if (more) {
+                                mbar_expect_tx(mbB, ROW_BYTES);
+                                bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
+                                if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
+                                if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                            }
+                        }
+                    });
+                    if (half == 0) {
+#pragma unroll
+                        for (int n1 = 0; n1 < 64; ++n1) {
+                            if (n1 <= rev64(n1)) {
+                                const pf2 u0 = pa_apply_pk<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1);
+                                const pf2 u1 = pa_apply_pk<PA>(x[n1], p0, sqrt_p0, a.pa_p1);
+                                x[n1] = u0;
+                                x[rev64(n1)] = u1;
+                            }
+                        }
+                    }
+                }
+                pf2 (&y)[64] = x;
+                mbar_wait_parity(mbA, phA);
+                phA ^= 1u;
+                {   // all loads before the first store: the compiler cannot prove rowA / accx_s disjoint
+                    pf2 hv[32], av[T64_ACC_SMEM > 0 ? T64_ACC_SMEM : 1];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) hv[i] = pk2(rowA[lane + 64 * i]);
+#pragma unroll
+                    for (int i = 0; i < T64_ACC_SMEM; ++i) av[i] = accx_s[i * FFT_THREADS];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int n1 = i < 16 ? i : i + 32;
+                        pf2 yv = y[rev64(n1)];
+                        if (i == 0 && lane == 0) yv = y[rev64(16)];
+                        if (i < T64_ACC_SMEM) av[i] = pcfma(yv, hv[i], av[i]);
+                        else acc[i] = pcfma(yv, hv[i], acc[i]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < T64_ACC_SMEM; ++i) accx_s[i * FFT_THREADS] = av[i];
+                }
+            }
+            // ---- the four groups' partial sums meet in the (idle) exchange buffers: fixed summation order ----
+            sy.x_sync();  // the group's last MAC has read its channel row
+#pragma unroll
+            for (int i = 0; i < 32; ++i) buf[lane + 64 * i] = i < T64_ACC_SMEM ? accx_s[i * FFT_THREADS] : acc[i];
+            __syncthreads();
+            pf2 accn[8];
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const int p = jp * 256 + t;
+                accn[jp] = padd(padd(bufs[p], bufs[4096 + p]), padd(bufs[2 * 4096 + p], bufs[3 * 4096 + p]));
+            }
+
+            // ---- end of pass: equalise / estimate distortion / slice / count (as k_link_frame) -----------
+            uint32_t detw[2] = {0u, 0u};
+            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
+            float2 nz[8];
+            if (first && !a.rx_eq_in) {
+                if (a.noise) {
+                    const float ns = a.noise_unit ? sc.noise_sigma : 1.0f;
+#pragma unroll
+                    for (int jp = 0; jp < 8; ++jp) {
+                        const float2 u = a.noise[(size_t)f * N_SC + jp * 256 + t];
+                        nz[jp] = make_float2(u.x * ns, u.y * ns);
+                    }
+                } else {
+                    const uint64_t fid = a.frame_id0 + f;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        uint32_t r[4];
+                        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_NOISE, (uint32_t)(t * 4 + q),
+                                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+                        const float2 g0 = box_muller(r[0], r[1]), g1 = box_muller(r[2], r[3]);
+                        nz[2 * q] = make_float2(g0.x * sc.noise_sigma, g0.y * sc.noise_sigma);
+                        nz[2 * q + 1] = make_float2(g1.x * sc.noise_sigma, g1.y * sc.noise_sigma);
+                    }
+                }
+            }
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const int p = jp * 256 + t;
+                const float2 ac = unpk(accn[jp]);
+                float2 corr;
+                if (first) {
+                    if (a.rx_eq_in) {
+                        corr = a.rx_eq_in[(size_t)f * N_SC + p];
+                    } else {
+                        const float2 r = make_float2(fmaf(64.f, nz[jp].x, ac.x), fmaf(64.f, nz[jp].y, ac.y));
+                        corr = cmul(r, ai[p]);
+                    }
+                    rxeq_s[p] = corr;
+                    if (a.rx_eq_out) a.rx_eq_out[(size_t)f * N_SC + p] = corr;
+                } else {
+                    const float2 z = cmul(ac, ai[p]);
+                    const float2 sy0 = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                    const float2 d = csub(z, sy0);   // distortion estimate, corrector.py:205
+                    corr = csub(rxeq_s[p], d);       // corrector.py:184
+                }
+                if (a.corr_out) a.corr_out[((size_t)f * (a.n_iter + 1) + pass) * N_SC + p] = corr;
+                const uint32_t idx = qam_detect(a.qam, corr);
+                detw[jp >> 2] |= idx << (8 * (jp & 3));
+            }
+            curw[0] = detw[0];
+            curw[1] = detw[1];
+            unsigned int nerr = __popc(detw[0] ^ txw[0]) + __popc(detw[1] ^ txw[1]);
+            nerr = __reduce_add_sync(0xffffffffu, nerr);
+            if ((t & 31) == 0) atomicAdd(&err_s[pass], nerr);
+            if (a.det_out) {
+                uint8_t* dp = a.det_out + ((size_t)f * (a.n_iter + 1) + pass) * N_SC;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) dp[jp * 256 + t] = (uint8_t)((detw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+            }
+        }
+        __syncthreads();
+        if (t <= a.n_iter) {
+            const unsigned int e = err_s[t];
+            err_s[t] = 0;
+            if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
+            atomicAdd(&a.err_total[t + (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u)], (unsigned long long)e);
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace mmimo

@@ -7,16 +7,18 @@ static double calc_alpha_host(double ibo_db) {  // modulation.py:178-189
 
 template <int PA>
 static void launch_frame(const FrameArgs& fa, const mmimo_ctx* c, int n) {
-    // Default: the two-pass radix-64 kernel (frame_kernel_r64.cuh).  MMIMO_FRAME_KERNEL=r16 selects the three-pass
-    // radix-16 kernel (measurement knob; same results to rounding, measured 4 % slower on the headline case).
-    const char* fk = getenv("MMIMO_FRAME_KERNEL");
-    if (!(fk && fk[0] == 'r' && fk[1] == '1')) {
+    // Default: the scaled-tangent radix-64 kernel (frame_kernel_t64.cuh).  MMIMO_FRAME_KERNEL=r64 / r16 (read once at
+    // mmimo_create) select the round-1 radix-64 kernel or the three-pass radix-16 kernel: measurement knobs, same
+    // results to rounding.
+    if (c->frame_kernel == 0) {
+        k_link_frame_t64<PA><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES, c->stream>>>(fa, c->tw_t64.as<float2>());
+        return;
+    }
+    if (c->frame_kernel == 1) {
         k_link_frame_r64<PA><<<std::min(n, c->n_sm), FFT_THREADS, FRAME64_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>());
         return;
     }
-    int per_sm = 2;
-    if (const char* e = getenv("MMIMO_CTAS_PER_SM")) per_sm = std::min(8, std::max(1, atoi(e)));  // measurement knob
-    const int grid = std::min(n, per_sm * c->n_sm);
+    const int grid = std::min(n, c->ctas_per_sm_r16 * c->n_sm);
     k_link_frame<PA><<<grid, FFT_THREADS, FRAME_SMEM_BYTES, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
 }
 
@@ -394,14 +396,6 @@ extern "C" int mmimo_sdr_simulate(mmimo_ctx* c, const mmimo_sdr_request* rq, dou
         c->hkvk_inv.reserve(chunk * N_SC * 8) || c->scal.reserve(chunk * sizeof(FrameScalars)) || c->alpha.reserve(chunk * K * 4) ||
         c->rx_pos.reserve(chunk * 24) || c->tx_idx.reserve(chunk * N_SC) || c->s_b.reserve(chunk * 16))
         return 1;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(k_sdr_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-        CK(cudaFuncSetAttribute(k_sdr_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-        CK(cudaFuncSetAttribute(k_sdr_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-        CK(cudaFuncSetAttribute(k_sdr_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-        attr_set = true;
-    }
     for (size_t c0 = 0; c0 < (size_t)rq->n_frames; c0 += chunk) {
         const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
         float2 *h_true = nullptr, *h_loop = nullptr;

@@ -15,6 +15,7 @@
 #include "prep_kernels.cuh"
 #include "mu_kernels.cuh"
 #include "frame_kernel_r64.cuh"
+#include "frame_kernel_t64.cuh"
 #include "stage_kernels.cuh"
 
 using namespace mmimo;
@@ -65,7 +66,11 @@ struct mmimo_ctx {
     int n_sm = 148;
     size_t scratch_budget = (size_t)12 << 30;
     // tables
-    DevBuf tw4096, tw256, freq_slot, freq_bin, tx_pos;
+    DevBuf tw4096, tw256, tw_t64, freq_slot, freq_bin, tx_pos;
+    // frame-kernel form, read once from MMIMO_FRAME_KERNEL at mmimo_create: 0 = scaled-tangent radix-64 (default),
+    // 1 = radix-64 with separate twiddle multiplies (round-1 form), 2 = three-pass radix-16; measurement knob only
+    int frame_kernel = 0;
+    int ctas_per_sm_r16 = 2;
     // per-chunk scratch
     DevBuf h_true, h_loop, csi_nz, rxeq_scr, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
@@ -144,6 +149,9 @@ extern "C" int mmimo_device_count(void) {
     return n;
 }
 
+static int create_body(mmimo_ctx* c);
+extern "C" void mmimo_destroy(mmimo_ctx* c);
+
 extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     if (!out) return fail("mmimo_create: out is NULL");
     *out = nullptr;
@@ -157,6 +165,16 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     mmimo_ctx* c = new mmimo_ctx();
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
+    if (const char* fk = getenv("MMIMO_FRAME_KERNEL")) c->frame_kernel = !strcmp(fk, "r64") ? 1 : !strcmp(fk, "r16") ? 2 : 0;
+    if (const char* e = getenv("MMIMO_CTAS_PER_SM")) c->ctas_per_sm_r16 = std::min(8, std::max(1, atoi(e)));
+    const int rc = create_body(c);
+    if (rc) { mmimo_destroy(c); return rc; }
+    *out = c;
+    return 0;
+}
+
+// everything of mmimo_create that can fail after the context exists (the caller destroys it on failure)
+static int create_body(mmimo_ctx* c) {
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
     // twiddle tables, computed in double (forward sign)
@@ -170,8 +188,11 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
             const double a = -2.0 * M_PI * (double)(k1 * n0) / 256.0;
             t2[k1 * 16 + n0] = make_float2((float)cos(a), (float)sin(a));
         }
-    if (c->tw4096.reserve(4096 * 8) || c->tw256.reserve(256 * 8) || c->counters.reserve(65 * 8)) { delete c; return 1; }
+    std::vector<float2> tt(t64::TAB_FLOAT2);
+    t64::build_table(tt.data());
+    if (c->tw4096.reserve(4096 * 8) || c->tw256.reserve(256 * 8) || c->tw_t64.reserve(t64::TAB_FLOAT2 * 8) || c->counters.reserve(65 * 8)) return 1;
     CK(cudaMemcpy(c->tw4096.p, t4.data(), 4096 * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->tw_t64.p, tt.data(), t64::TAB_FLOAT2 * 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(c->tw256.p, t2.data(), 256 * 8, cudaMemcpyHostToDevice));
     CK(cudaMemset(c->counters.p, 0, 65 * 8));
     CK(cudaFuncSetAttribute(k_link_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES));
@@ -182,21 +203,35 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     CK(cudaFuncSetAttribute(k_link_frame_r64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_r64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_r64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME64_SMEM_BYTES));
-    if (stage_kernels_init()) { delete c; return 1; }
-    *out = c;
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    // the two-user and SDR kernels: per device, so set for every context (not once per process)
+    CK(cudaFuncSetAttribute(k_link_frame<PA_NONE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_SOFT_LIMITER, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_RAPP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame<PA_TOI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_sdr_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_sdr_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_sdr_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_sdr_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
+    if (stage_kernels_init()) return 1;
     return 0;
 }
 
 extern "C" void mmimo_destroy(mmimo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
-    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->rxeq_scr, &c->v, &c->sscale, &c->agc_inv,
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    c->prof_recs.clear();
+    DevBuf* all[] = {&c->tw4096, &c->tw256, &c->tw_t64, &c->sweep_tab, &c->sweep_cnt, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->rxeq_scr, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,
                      &c->s_a, &c->s_b, &c->s_c, &c->s_d};
     for (DevBuf* b : all) b->release();
-    cudaStreamDestroy(c->own_stream);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
 

@@ -3,11 +3,6 @@
 
 template <int PA>
 static void launch_frame_mu(const FrameArgs& fa, const mmimo_ctx* c, int n) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_link_frame<PA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU);
-        attr_set = true;
-    }
     const int grid = std::min(n, 2 * c->n_sm);
     k_link_frame<PA, true><<<grid, FFT_THREADS, FRAME_SMEM_BYTES_MU, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
 }
