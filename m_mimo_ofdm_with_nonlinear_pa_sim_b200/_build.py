@@ -34,18 +34,33 @@ def nvcc_path() -> str:
     raise RuntimeError("nvcc not found: cannot build libmmimo_b200.so")
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
-        return LIB_PATH
-    cmd = [nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-           "-Xptxas", "-v" if verbose else "-warn-spills", "-shared", "-Xcompiler", "-fPIC",
-           "-o", LIB_PATH] + SOURCES
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if verbose:
-        sys.stderr.write(res.stderr)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n%s\n%s" % (" ".join(cmd), res.stderr))
-    return LIB_PATH
+def build(force: bool = False, verbose: bool = False, defines=(), out_path: str = None) -> str:
+    """Compile the library.  Several processes may get here at once (torchrun ranks, spawned `main_mp_*` workers on a
+    fresh checkout): the build runs under an exclusive lock, staleness is re-checked once the lock is held, nvcc writes
+    to a temporary file in the same directory and the result is renamed into place, so nobody dlopens a half-written
+    library.  `defines` / `out_path` build measurement variants (tools/build_variants.py) next to the product library."""
+    import fcntl
+    out = out_path or LIB_PATH
+    if out_path is None and not force and not is_stale():
+        return out
+    with open(os.path.join(PKG_DIR, ".build.lock"), "w") as lock:
+        if out_path is None:  # variants go to their own files and may build concurrently
+            fcntl.flock(lock, fcntl.LOCK_EX)
+        if out_path is None and not force and not is_stale():  # another process built it while we waited
+            return out
+        tmp = "%s.tmp.%d" % (out, os.getpid())
+        cmd = [nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+               "-Xptxas", "-v" if verbose else "-warn-spills", "-shared", "-Xcompiler", "-fPIC"]
+        cmd += ["-D" + d for d in defines] + ["-o", tmp] + SOURCES
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if verbose:
+            sys.stderr.write(res.stderr)
+        if res.returncode != 0:
+            if os.path.exists(tmp):
+                os.unlink(tmp)
+            raise RuntimeError("nvcc failed:\n%s\n%s" % (" ".join(cmd), res.stderr))
+        os.replace(tmp, out)
+    return out
 
 
 if __name__ == "__main__":

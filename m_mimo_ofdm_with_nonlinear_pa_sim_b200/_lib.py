@@ -68,7 +68,8 @@ EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_er
 
 
 def lib_path() -> str:
-    return _build.LIB_PATH
+    """The in-tree library; MMIMO_LIB points at a measurement variant built by tools/build_variants.py instead."""
+    return os.environ.get("MMIMO_LIB") or _build.LIB_PATH
 
 
 def load(build_if_missing: bool = True):
@@ -77,12 +78,15 @@ def load(build_if_missing: bool = True):
     if _LIB is not None:
         return _LIB
     path = lib_path()
-    if build_if_missing and _build.is_stale():
+    if build_if_missing and not os.environ.get("MMIMO_LIB") and _build.is_stale():
         try:
             _build.build()
         except Exception as exc:  # no nvcc on this box: a prebuilt .so is still fine
             if not os.path.isfile(path):
                 raise MmimoError("libmmimo_b200.so is missing and could not be built: %s" % exc) from exc
+            import warnings
+            warnings.warn("libmmimo_b200.so is older than its sources and could not be rebuilt (%s): using the stale "
+                          "library" % str(exc).splitlines()[0])
     if not os.path.isfile(path):
         raise MmimoError("libmmimo_b200.so not found at %s - run `python __graft_entry__.py build`" % path)
     lib = C.CDLL(path)

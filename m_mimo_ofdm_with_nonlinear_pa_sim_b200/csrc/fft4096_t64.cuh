@@ -154,7 +154,8 @@ struct RTw {
 
 // Radix-4 butterfly, forward sign, twiddles on inputs 1..3:  y_r = sum_m (w_m a_m) (-j)^(m r),  w_0 = 1.
 // Outputs in place (a_r <- y_r).  11 packed FMAs (8 when the twiddles are trivial).
-template <class TW>
+// OUT: bit r set <=> output y_r is needed (pruned last level of the frame kernel's second transform).
+template <class TW, int OUT = 15>
 T64_HD void bf4_tw(pf2& a0, pf2& a1, pf2& a2, pf2& a3, const TW& tw) {
     bool skip1 = false, skip2 = false, skip3 = false;
     if (TW::kConst) {
@@ -182,15 +183,15 @@ T64_HD void bf4_tw(pf2& a0, pf2& a1, pf2& a2, pf2& a3, const TW& tw) {
         d13 = qfma_jp<dp>(a3, -tw.rho, a1);
     }
     if (TW::kConst && TW::p1 == 0 && tw.f1 == 1.f) {
-        a0 = qadd(s02, s13);
-        a2 = qsub(s02, s13);
+        if (OUT & 1) a0 = qadd(s02, s13);
+        if (OUT & 4) a2 = qsub(s02, s13);
     } else {
-        a0 = qfma_jp<TW::p1>(s13, tw.f1, s02);
-        a2 = qfma_jp<TW::p1>(s13, -tw.f1, s02);
+        if (OUT & 1) a0 = qfma_jp<TW::p1>(s13, tw.f1, s02);
+        if (OUT & 4) a2 = qfma_jp<TW::p1>(s13, -tw.f1, s02);
     }
     // y1 = d02 + (-j) j^p1 f1 d13',  y3 = d02 - (-j) j^p1 f1 d13'
-    a1 = qfma_jp<TW::p1 - 1>(d13, tw.f1, d02);
-    a3 = qfma_jp<TW::p1 - 1>(d13, -tw.f1, d02);
+    if (OUT & 2) a1 = qfma_jp<TW::p1 - 1>(d13, tw.f1, d02);
+    if (OUT & 8) a3 = qfma_jp<TW::p1 - 1>(d13, -tw.f1, d02);
 }
 
 // ---- per-lane table of pass 2 (host-built, double precision) ------------------------------------------------
@@ -292,17 +293,37 @@ template <int... B>
 T64_HD void p1_level_c_all(pf2 (&x)[64], std::integer_sequence<int, B...>) {
     (p1_level_c<B>(x), ...);
 }
-// PRUNE_IN: registers 17..47 are known to be zero (values ignored); register 16 is honoured only when `stray`
-// (lane 0 carries the stray bin there, see frame_kernel_t64.cuh)
-T64_HD void radix64_const(pf2 (&x)[64]) {
+T64_HD void p1_level_a(pf2 (&x)[64]) {
     const CTw<0, 0, 0> tw0{};
 #pragma unroll
     for (int q = 0; q < 16; ++q) bf4_tw(x[q], x[q + 16], x[q + 32], x[q + 48], tw0);
+}
+// level A when registers 17..47 are known to be zero (guard band of the frame kernel's first transform; register 16
+// may be non-zero: lane 0 carries the stray bin there, frame_kernel_t64.cuh): y_r = a0 + j^r a3, 4 instead of 8
+// instructions per butterfly.  The values of registers 17..47 on entry are ignored.
+T64_HD void p1_level_a_pruned(pf2 (&x)[64]) {
+    const CTw<0, 0, 0> tw0{};
+    x[32] = qpk(0.f, 0.f);
+    bf4_tw(x[0], x[16], x[32], x[48], tw0);
+#pragma unroll
+    for (int q = 1; q < 16; ++q) {
+        const pf2 a0 = x[q], a3 = x[q + 48];
+        x[q] = qadd(a0, a3);
+        x[q + 16] = qfma_js(a3, 1.f, a0);
+        x[q + 32] = qsub(a0, a3);
+        x[q + 48] = qfma_js(a3, -1.f, a0);
+    }
+}
+T64_HD void p1_levels_bc(pf2 (&x)[64]) {
     p1_level_b<0>(x);
     p1_level_b<1>(x);
     p1_level_b<2>(x);
     p1_level_b<3>(x);
     p1_level_c_all(x, std::make_integer_sequence<int, 16>());
+}
+T64_HD void radix64_const(pf2 (&x)[64]) {
+    p1_level_a(x);
+    p1_levels_bc(x);
 }
 
 // ---- pass 2: run-time twiddles from the per-lane table ------------------------------------------------------------
@@ -312,24 +333,27 @@ T64_HD void p2_level_b(pf2 (&x)[64], const Raw3& raw) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) bf4_tw(x[16 * R + q], x[16 * R + q + 4], x[16 * R + q + 8], x[16 * R + q + 12], tw);
 }
-template <int B>
+// PRUNE_OUT: only outputs r'' = 0 and 3 (k1 = 0..15, 48..63: the data bins) are produced, plus r'' = 1 of class 0
+// (k1 = 16: bin 1024 of lane 0); the other registers hold garbage afterwards.
+template <int B, bool PRUNE_OUT = false>
 T64_HD void p2_level_c(pf2 (&x)[64], const Raw3& raw) {
     const auto tw = as_tw<form_c(B, 1), form_c(B, 2), form_c(B, 3)>(raw);
     constexpr int base = 16 * (B & 3) + 4 * (B >> 2);
-    bf4_tw(x[base], x[base + 1], x[base + 2], x[base + 3], tw);
+    using TW = RTw<form_c(B, 1), form_c(B, 2), form_c(B, 3)>;
+    bf4_tw<TW, PRUNE_OUT ? (B == 0 ? 11 : 9) : 15>(x[base], x[base + 1], x[base + 2], x[base + 3], tw);
 }
 // level C with the table entries fetched DEPTH classes ahead of the butterfly that uses them
-template <int DEPTH, int B>
+template <int DEPTH, int B, bool PRUNE_OUT = false>
 struct P2LevelC {
     static T64_HD void run(pf2 (&x)[64], Raw3 (&ring)[DEPTH], const float2* __restrict__ tab, const int lane) {
         const Raw3 cur = ring[B % DEPTH];
         if (B + DEPTH < 16) ring[B % DEPTH] = load_raw(tab + TAB_C, 1024, lane + 64 * (B + DEPTH));
-        p2_level_c<B>(x, cur);
-        P2LevelC<DEPTH, B + 1>::run(x, ring, tab, lane);
+        p2_level_c<B, PRUNE_OUT>(x, cur);
+        P2LevelC<DEPTH, B + 1, PRUNE_OUT>::run(x, ring, tab, lane);
     }
 };
-template <int DEPTH>
-struct P2LevelC<DEPTH, 16> {
+template <int DEPTH, bool PRUNE_OUT>
+struct P2LevelC<DEPTH, 16, PRUNE_OUT> {
     static T64_HD void run(pf2 (&)[64], Raw3 (&)[DEPTH], const float2* __restrict__, const int) {}
 };
 
@@ -338,42 +362,70 @@ struct TabA {  // level-A entry of this lane, loaded once per kernel (the same f
 };
 T64_HD TabA load_tab_a(const float2* __restrict__ tab, const int lane) { return TabA{load_raw(tab + TAB_A, 64, lane)}; }
 
-template <int DEPTH>
-T64_HD void radix64_table(pf2 (&x)[64], const float2* __restrict__ tab, const TabA& ta, const int lane) {
-    Raw3 rb[4];
+// level A of pass 2 (the table entries of level B are fetched first and returned in rb)
+T64_HD void p2_level_a(pf2 (&x)[64], Raw3 (&rb)[4], const float2* __restrict__ tab, const TabA& ta, const int lane) {
 #pragma unroll
     for (int r = 0; r < 4; ++r) rb[r] = load_raw(tab + TAB_B, 256, lane + 64 * r);
-    {
-        const auto tw = as_tw<0, 0, 0>(ta.raw);
+    const auto tw = as_tw<0, 0, 0>(ta.raw);
 #pragma unroll
-        for (int q = 0; q < 16; ++q) bf4_tw(x[q], x[q + 16], x[q + 32], x[q + 48], tw);
-    }
-    Raw3 ring[DEPTH];
+    for (int q = 0; q < 16; ++q) bf4_tw(x[q], x[q + 16], x[q + 32], x[q + 48], tw);
+}
+// level B of pass 2; `ring` comes back holding the first DEPTH level-C table entries
+template <int DEPTH>
+T64_HD void p2_level_b_all(pf2 (&x)[64], const Raw3 (&rb)[4], Raw3 (&ring)[DEPTH], const float2* __restrict__ tab,
+                           const int lane) {
 #pragma unroll
     for (int b = 0; b < DEPTH; ++b) ring[b] = load_raw(tab + TAB_C, 1024, lane + 64 * b);
     p2_level_b<0>(x, rb[0]);
     p2_level_b<1>(x, rb[1]);
     p2_level_b<2>(x, rb[2]);
     p2_level_b<3>(x, rb[3]);
-    P2LevelC<DEPTH, 0>::run(x, ring, tab, lane);
+}
+template <int DEPTH>
+T64_HD void p2_levels_ab(pf2 (&x)[64], Raw3 (&ring)[DEPTH], const float2* __restrict__ tab, const TabA& ta,
+                         const int lane) {
+    Raw3 rb[4];
+    p2_level_a(x, rb, tab, ta, lane);
+    p2_level_b_all<DEPTH>(x, rb, ring, tab, lane);
+}
+template <int DEPTH, bool PRUNE_OUT>
+T64_HD void p2_level_c_all(pf2 (&x)[64], Raw3 (&ring)[DEPTH], const float2* __restrict__ tab, const int lane) {
+    P2LevelC<DEPTH, 0, PRUNE_OUT>::run(x, ring, tab, lane);
+}
+template <int DEPTH>
+T64_HD void radix64_table(pf2 (&x)[64], const float2* __restrict__ tab, const TabA& ta, const int lane) {
+    Raw3 ring[DEPTH];
+    p2_levels_ab<DEPTH>(x, ring, tab, ta, lane);
+    p2_level_c_all<DEPTH, false>(x, ring, tab, lane);
 }
 
 // ---- the two halves of a transform (the device wrapper puts the group barriers between them) -------------------
+// Exchange layout: element (k0, n0) of the 64 x 64 intermediate lives at buf[k0 * T64_ROW + n0] with T64_ROW = 65
+// (one float2 of padding per row).  Stores (lane = n0, 64 consecutive 8-byte words per k0) and loads (lane = k0,
+// stride 65 words: 16 lanes of a half-warp hit 16 different bank pairs) are both conflict-free, and every address
+// is `lane-dependent base + compile-time offset`: no per-access integer instructions (the XOR swizzle this replaces
+// cost a LOP3 and an IADD3 per access, ~10 % of the issue slots of a transform).
+#ifndef T64_ROW
+#define T64_ROW 65
+#endif
+constexpr int XROW = T64_ROW;
+constexpr int XBUF = 64 * XROW;  // float2 elements of one group's exchange buffer
+T64_HD int xidx(const int k0, const int n0) { return XROW == 64 ? k0 * 64 + (n0 ^ k0) : k0 * XROW + n0; }
 // pass 1 + exchange stores.  x in: x[n1] = element lane + 64 n1.
+T64_HD void exchange_store(const pf2 (&x)[64], pf2* __restrict__ buf, const int lane) {
+#pragma unroll
+    for (int p = 0; p < 64; ++p) buf[xidx(rev64(p), lane)] = x[p];
+}
 T64_HD void pass1_store(pf2 (&x)[64], pf2* __restrict__ buf, const int lane) {
     radix64_const(x);
-#pragma unroll
-    for (int p = 0; p < 64; ++p) {
-        const int k0 = rev64(p);
-        buf[k0 * 64 + (lane ^ k0)] = x[p];
-    }
+    exchange_store(x, buf, lane);
 }
 // exchange loads (in the order level A consumes them)
 T64_HD void pass2_load(pf2 (&x)[64], const pf2* __restrict__ buf, const int lane) {
 #pragma unroll
     for (int q = 0; q < 16; ++q)
 #pragma unroll
-        for (int m = 0; m < 4; ++m) x[q + 16 * m] = buf[lane * 64 + ((q + 16 * m) ^ lane)];
+        for (int m = 0; m < 4; ++m) x[q + 16 * m] = buf[xidx(lane, q + 16 * m)];
 }
 // pass 2.  x out: X[bin lane + 64 k1] in x[rev64(k1)].
 template <int DEPTH>

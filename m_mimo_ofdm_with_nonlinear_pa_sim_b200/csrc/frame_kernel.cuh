@@ -60,6 +60,11 @@ struct FrameArgs {
     int loop_single_user;
     // multi-point batches (mmimo_link_sweep): frame f counts into err_total[64 * ((frame0 + f) / fpp) + iteration]
     int fpp; unsigned frame0;
+    // k_link_frame_t64 only: cycles by which antenna groups 2 and 3 start every pass after groups 0 and 1.  The two
+    // warps that share a scheduler belong to groups g and g + 2; started together they run the same instruction
+    // stream in lock-step, so their shared-memory exchange phases (no FMA work) coincide.  The offset makes one warp's
+    // exchange overlap the other's butterflies (frame_kernel_t64.cuh).
+    int stagger;
 };
 
 constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048;

@@ -25,23 +25,54 @@ namespace mmimo {
 #ifndef T64_ACC_SMEM
 #define T64_ACC_SMEM 12  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
 #endif
+#ifndef T64_PRUNE
+#define T64_PRUNE 1  // guard-band pruning of the first transform's level A and of the second transform's last level
+#endif
+#ifndef T64_LOOP
+#define T64_LOOP 1  // 1: guard-band form of level A of the first transform ahead of the loop; 2: loop starts with level A
+#endif
+#ifndef T64_SYNC
+#define T64_SYNC 1  // group-barrier placement, see the kernel
+#endif
+#ifndef T64_PA_UNIT
+#define T64_PA_UNIT 1  // PA evaluated on the signal scaled to a unit threshold (one multiply less per sample)
+#endif
 constexpr int FRAME_T64_SMEM_BYTES =
-    (4096 + R64_GROUPS * 4096 + 2 * N_SC + T64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
+    (4096 + R64_GROUPS * t64::XBUF + 2 * N_SC + T64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
 static_assert(FRAME_T64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
+
+// PA on one packed sample.  T64_PA_UNIT: the sample arrives scaled so that the threshold is 1 (see the kernel):
+// soft limiter g = rsqrt(max(|x|^2, 1)); Rapp g = (1 + |x|^(2p))^(-1/(2p)); third order g = 1 - |x|^2.
+template <int KIND>
+__device__ __forceinline__ pf2 pa_apply_t64(pf2 xp, const float p0, const float sqrt_p0, const float p1) {
+    if (!T64_PA_UNIT) return pa_apply_pk<KIND>(xp, p0, sqrt_p0, p1);
+    if (KIND == PA_NONE) return xp;
+    const float2 x = unpk(xp);
+    const float p = fmaf(x.x, x.x, x.y * x.y);
+    float g;
+    if (KIND == PA_SOFT_LIMITER) {
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(g) : "f"(fmaxf(p, 1.0f)));  // rsqrt(1) = 1 exactly: no clipping below 1
+    } else if (KIND == PA_RAPP) {
+        g = __powf(1.0f + __powf(p, p1), -0.5f / p1);
+    } else {
+        g = 1.0f - p;
+    }
+    return pmul(xp, pbc(g));
+}
 
 template <int PA>
 __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameArgs a, const float2* __restrict__ tab_g) {
     extern __shared__ __align__(128) float2 smem[];
     float2* tab = smem;                                         // per-lane twiddle parameters (t64::build_table)
-    pf2* bufs = reinterpret_cast<pf2*>(smem + 4096);            // [group][4096]
-    float2* symn_s = smem + 4096 + R64_GROUPS * 4096;           // scaled current symbols, native slots
+    pf2* bufs = reinterpret_cast<pf2*>(smem + 4096);            // [group][t64::XBUF]
+    float2* symn_s = smem + 4096 + R64_GROUPS * t64::XBUF;      // scaled current symbols, native slots
     unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC + T64_ACC_SMEM * FFT_THREADS);
     unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
     float2* rxeq_s = reinterpret_cast<float2*>(mbar_s + 2 * R64_GROUPS);  // equalised received signal of the frame
 
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
     pf2* accx_s = reinterpret_cast<pf2*>(symn_s + N_SC) + t;    // accumulators i < T64_ACC_SMEM at [i * 256]
-    pf2* buf = bufs + g * 4096;
+    pf2* buf = bufs + g * t64::XBUF;
     const float2* rowA = reinterpret_cast<const float2*>(buf);   // channel row of the antenna being accumulated
     const float2* rowB = rowA + N_SC;                            // precoder / CSI row of the group's next antenna
     const unsigned mbA = smem_u32(mbar_s + 2 * g), mbB = mbA + 8;  // completion of the rowA / rowB copies
@@ -88,13 +119,17 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
             const bool explicit_v = sd.v != nullptr;
             const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
             const float sqrt_p0 = sqrtf(p0);
+            // T64_PA_UNIT: the chain runs on x / sqrt(P) (P = saturation power; third order: 1 / cubic coefficient), so the
+            // PA compares against 1 and needs no per-sample multiply by sqrt(P); the factor returns after the antenna sum
+            const float pa_out_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? 1.0f / sqrt_p0 : sqrt_p0;
+            const float pa_in_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? sqrt_p0 : 1.0f / sqrt_p0;
             {
                 const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs;
 #pragma unroll
                 for (int jp = 0; jp < 8; ++jp) {
                     const int p = jp * 256 + t;
                     const float2 s = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
-                    const float gsc = ss[p];
+                    const float gsc = ss[p] * pa_in_scale;
                     symn_s[p] = make_float2(s.x * gsc, s.y * gsc);
                 }
             }
@@ -110,6 +145,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     bulk_prefetch_l2(Hm + (size_t)g * N_SC, ROW_BYTES);
                     if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
                 }
+            }
+            if (a.stagger > 0 && g >= 2 && K > 2) {  // de-phase the two warps of every scheduler (FrameArgs::stagger)
+                const long long t0 = clock64();
+                while (clock64() - t0 < a.stagger) {}
             }
             pf2 acc[32];  // partial sum over this group's antennas (entries < T64_ACC_SMEM unused: in accx_s)
 #pragma unroll
@@ -130,41 +169,77 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     if (explicit_v) x[n1] = pcmul(h, s.x, s.y);                                 // v * s
                     else x[n1] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));               // conj(h) * s
                 }
+                if (T64_LOOP != 1) {
 #pragma unroll
-                for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
+                    for (int n1 = 16; n1 < 48; ++n1) x[n1] = pk(0.f, 0.f);
+                } else {
+                    x[16] = pk(0.f, 0.f);
+                }
                 if (lane == 0) { x[16] = x[0]; x[0] = pk(0.f, 0.f); }
-                sy.x_sync();  // rows fully consumed by the whole group before the exchange overwrites them
-                // ONE transform body serves both transforms of the chain (two specialised, pruned bodies do not fit
-                // the instruction cache next to each other, profiles/r01_r64_frame_kernel.txt); the digit reversal
-                // between them is folded into the destination registers of the PA.
-#pragma unroll 1
-                for (int half = 0; half < 2; ++half) {
-                    fft4096_t64<T64_DEPTH>(x, buf, tab, tab_a, lane, sy, [&]() {
-                        if (half == 1 && lane == 0) {
-                            const bool more = k + R64_GROUPS < K;
-                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                            mbar_expect_tx(mbA, ROW_BYTES);
-                            bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
-                            if (more) {
-                                mbar_expect_tx(mbB, ROW_BYTES);
-                                bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
-                                if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
-                                if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
-                            }
-                        }
-                    });
-                    if (half == 0) {
-#pragma unroll
-                        for (int n1 = 0; n1 < 64; ++n1) {
-                            if (n1 <= rev64(n1)) {
-                                const pf2 u0 = pa_apply_pk<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1);
-                                const pf2 u1 = pa_apply_pk<PA>(x[n1], p0, sqrt_p0, a.pa_p1);
-                                x[n1] = u0;
-                                x[rev64(n1)] = u1;
-                            }
+                // ONE loop body serves both transforms of the chain (two specialised bodies do not fit the instruction
+                // cache next to each other, profiles/r01_r64_frame_kernel.txt); what differs between the transforms sits
+                // outside the shared part: the guard-band form of level A of pass 1 (first transform, T64_LOOP 1), the
+                // PA with the digit reversal folded into its destination registers, and the pruned last level of pass 2
+                // (second transform), which follows the loop so that no register shuffle is needed on the way out.
+                // Group barriers: S1 = everybody has finished READING the buffer (rows of the precode / previous
+                // exchange) before it is overwritten; S2 = all stores visible; S3 (second transform only) = all loads done
+                // before the TMA rows land in the buffer.  With T64_SYNC 1, S1 and S3 sit after long compute phases where
+                // nobody waits, and the exchange loads overlap the first butterflies of pass 2.
+                auto issue_rows = [&]() {
+                    if (lane == 0) {  // the exchange buffer is idle from here to the next chain's stores
+                        const bool more = k + R64_GROUPS < K;
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_expect_tx(mbA, ROW_BYTES);
+                        bulk_g2s(smem_u32(rowA), Hm + (size_t)k * N_SC, ROW_BYTES, mbA);
+                        if (more) {
+                            mbar_expect_tx(mbB, ROW_BYTES);
+                            bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
+                            if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
+                            if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
                         }
                     }
+                };
+                auto pa_all = [&]() {
+#pragma unroll
+                    for (int n1 = 0; n1 < 64; ++n1) {
+                        if (n1 <= rev64(n1)) {
+                            const pf2 u0 = pa_apply_t64<PA>(x[rev64(n1)], p0, sqrt_p0, a.pa_p1);
+                            const pf2 u1 = pa_apply_t64<PA>(x[n1], p0, sqrt_p0, a.pa_p1);
+                            x[n1] = u0;
+                            x[rev64(n1)] = u1;
+                        }
+                    }
+                };
+                if (!T64_SYNC) sy.x_sync();  // S1 of the first transform
+                if (T64_LOOP == 1) t64::p1_level_a_pruned(x);
+                t64::Raw3 ring[T64_DEPTH];
+#pragma unroll 1
+                for (int half = 0;; ++half) {
+                    if (T64_LOOP != 1) t64::p1_level_a(x);
+                    t64::p1_levels_bc(x);
+                    if (T64_SYNC) sy.x_sync();  // S1
+                    t64::exchange_store(x, buf, lane);
+                    sy.x_sync();                // S2
+                    t64::pass2_load(x, buf, lane);
+                    t64::Raw3 rb[4];
+                    if (!T64_SYNC) {
+                        sy.x_sync();            // S3 (both transforms)
+                        if (half == 1) issue_rows();
+                        t64::p2_level_a(x, rb, tab, tab_a, lane);
+                    } else {
+                        t64::p2_level_a(x, rb, tab, tab_a, lane);
+                        if (half == 1) {
+                            sy.x_sync();        // S3
+                            issue_rows();
+                        }
+                    }
+                    t64::p2_level_b_all<T64_DEPTH>(x, rb, ring, tab, lane);
+                    if (half == 1) break;
+                    t64::p2_level_c_all<T64_DEPTH, false>(x, ring, tab, lane);
+                    pa_all();
+                    if (T64_LOOP == 1) t64::p1_level_a(x);
                 }
+                t64::p2_level_c_all<T64_DEPTH, T64_PRUNE != 0>(x, ring, tab, lane);
                 pf2 (&y)[64] = x;
                 mbar_wait_parity(mbA, phA);
                 phA ^= 1u;
@@ -195,7 +270,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
 #pragma unroll
             for (int jp = 0; jp < 8; ++jp) {
                 const int p = jp * 256 + t;
-                accn[jp] = padd(padd(bufs[p], bufs[4096 + p]), padd(bufs[2 * 4096 + p], bufs[3 * 4096 + p]));
+                accn[jp] = padd(padd(bufs[p], bufs[t64::XBUF + p]), padd(bufs[2 * t64::XBUF + p], bufs[3 * t64::XBUF + p]));
+                if (T64_PA_UNIT) accn[jp] = pmul(accn[jp], pbc(pa_out_scale));
             }
 
             // ---- end of pass: equalise / estimate distortion / slice / count (as k_link_frame) -----------

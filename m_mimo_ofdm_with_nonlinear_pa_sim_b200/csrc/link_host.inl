@@ -82,7 +82,8 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ca.h_out = h_true; ca.n_ant = K;
         // MRT from this very channel (no CSI error, no separate channel knowledge) and enough realisations to fill the
         // GPU with one CTA each: the channel kernel also writes the symbol scale, the realisation kernel skips a pass
-        sscale_ready = !in.h_loop && !(rq->csi_eps > 0.0) && n >= 2 * c->n_sm;
+        const bool los_closed_form = c->prep_analytic && cfg.channel_kind == MMIMO_CHAN_LOS && !cfg.skip_attenuation && !want_v;
+        sscale_ready = !in.h_loop && !(rq->csi_eps > 0.0) && n >= 2 * c->n_sm && !los_closed_form;
         ca.sscale_out = sscale_ready ? c->sscale.as<float>() : nullptr;
         prof_begin(c, PROF_CHAN);
         k_gen_channel<<<dim3(sscale_ready ? 1 : (K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), 256, 0, c->stream>>>(ca);
@@ -121,6 +122,30 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         xa.seed = rq->seed; xa.frame_id0 = rq->frame_id0 + c0; xa.stream = in.csi_stream; xa.n_ant = K;
         k_csi_error<<<dim3(K, n), 256, 0, c->stream>>>(xa);
         c->launches++;
+    }
+    // line of sight + MRT from the true channel: closed form in the K path amplitudes, no pass over the channel rows
+    const bool analytic = c->prep_analytic && !in.h_true && cfg.channel_kind == MMIMO_CHAN_LOS && !cfg.skip_attenuation &&
+                          h_loop == h_true && !want_v;
+    if (analytic) {
+        PrepLosArgs la{};
+        la.tx_pos = c->tx_pos.as<double>(); la.rx_pos = c->rx_pos.as<double>(); la.freq_slot = c->freq_slot.as<double>();
+        la.gain_lin = sqrt(pow(10.0, cfg.ant_gain_db / 10.0));
+        la.sscale = c->sscale.as<float>(); la.agc_inv = c->agc_inv.as<float2>(); la.hkvk_inv = c->hkvk_inv.as<float2>();
+        la.scal = c->scal.as<FrameScalars>(); la.alpha_out = c->alpha.as<float>();
+        la.n_ant = K; la.pa_kind = cfg.pa_kind; la.is_mcnc = cfg.receiver_kind == MMIMO_RX_MCNC;
+        la.ibo_lin = pow(10.0, cfg.ibo_db / 10.0);
+        la.avg_symbol_power = avg_symbol_power(cfg.constel_size);
+        la.avg_sample_power = la.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
+        la.snr_lin = pow(10.0, rq->snr_db / 10.0);
+        SweepArgs sw{c->sweep.snr_lin, c->sweep.ibo_lin, c->sweep.fpp, (unsigned)c0, 0};
+        prof_begin(c, PROF_PREP);
+        if (sw.fpp) k_prep_los<true><<<n, 256, 0, c->stream>>>(la, sw);
+        else k_prep_los<false><<<n, 256, 0, c->stream>>>(la, sw);
+        prof_end(c);
+        c->launches++;
+        *h_true_out = h_true;
+        *h_loop_out = h_loop;
+        return 0;
     }
     PrepArgs pa{};
     pa.h_loop = h_loop; pa.h_fs = (long long)K * N_SC;
@@ -250,6 +275,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.n_iter = I;
         fa.qam.log2side = log2_side(cfg.constel_size);
         fa.n_frames = n;
+        fa.stagger = c->t64_stagger;
         fa.tx_idx = nullptr; fa.noise = nullptr;
         if (rq->tx_idx) {
             if (upload_native<uint8_t>(c, rq->tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;

@@ -70,6 +70,10 @@ struct mmimo_ctx {
     // frame-kernel form, read once from MMIMO_FRAME_KERNEL at mmimo_create: 0 = scaled-tangent radix-64 (default),
     // 1 = radix-64 with separate twiddle multiplies (round-1 form), 2 = three-pass radix-16; measurement knob only
     int frame_kernel = 0;
+    // start offset (SM cycles) of antenna groups 2,3 of k_link_frame_t64 (FrameArgs::stagger); MMIMO_T64_STAGGER overrides
+    int t64_stagger = 0;
+    // closed-form realisation kernel for LOS + MRT (k_prep_los); MMIMO_PREP_ANALYTIC=0 keeps k_prep_realisation (A/B knob)
+    int prep_analytic = 1;
     int ctas_per_sm_r16 = 2;
     // per-chunk scratch
     DevBuf h_true, h_loop, csi_nz, rxeq_scr, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
@@ -166,6 +170,8 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
     if (const char* fk = getenv("MMIMO_FRAME_KERNEL")) c->frame_kernel = !strcmp(fk, "r64") ? 1 : !strcmp(fk, "r16") ? 2 : 0;
+    if (const char* e = getenv("MMIMO_PREP_ANALYTIC")) c->prep_analytic = atoi(e) != 0;
+    if (const char* e = getenv("MMIMO_T64_STAGGER")) c->t64_stagger = std::max(0, atoi(e));
     if (const char* e = getenv("MMIMO_CTAS_PER_SM")) c->ctas_per_sm_r16 = std::min(8, std::max(1, atoi(e)));
     const int rc = create_body(c);
     if (rc) { mmimo_destroy(c); return rc; }

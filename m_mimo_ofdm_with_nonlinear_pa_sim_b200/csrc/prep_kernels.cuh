@@ -302,6 +302,77 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
 }
 
 // ---------------------------------------------------------------------------------------------
+// k_prep_los: the work of k_prep_realisation in CLOSED FORM for a line-of-sight channel with MRT precoding from the
+// true channel (the headline configuration: main_mp_miso_mcnc_ber_vs_ebn0.py).  With h_k[s] = a_k / f_s * e^(j phi)
+// (channel.py:56-66, a_k = gain c / (4 pi d_k)) every quantity of antenna_array.py:163-171, :313-360 and
+// mp_model.py:290-329 depends on the K amplitudes only:
+//     ||h[:, s]||^2 = A / f_s^2,  A = sum_k a_k^2          v_k[s] = conj(h_k[s]) f_s / sqrt(A),  |v_k[s]|^2 = a_k^2 / A
+//     vk_pow[k] = N_sc a_k^2 / A   ->  ibo_k, alpha_k      sum_k h_k v_k = sqrt(A) / f_s
+//     sum_k alpha_k h_k v_k = S1 / (f_s sqrt(A)),  S1 = sum_k alpha_k a_k^2        mean |v|^2 = 1 / K
+// so no pass over the [F][K][2048] channel rows is needed (k_prep_realisation reads them twice: 1.6 ms per 4144
+// frames at K = 64).  One CTA per realisation; receiver positions come from the buffer k_gen_channel read or wrote.
+// ---------------------------------------------------------------------------------------------
+struct PrepLosArgs {
+    const double* tx_pos;     // [K][3]
+    const double* rx_pos;     // [F][3]
+    const double* freq_slot;  // [2048]
+    double gain_lin;
+    float* sscale; float2* agc_inv; float2* hkvk_inv; FrameScalars* scal; float* alpha_out;
+    int n_ant, pa_kind, is_mcnc;
+    double ibo_lin, avg_symbol_power, avg_sample_power, snr_lin;
+};
+
+template <bool SWEEP>
+__global__ void __launch_bounds__(256) k_prep_los(const PrepLosArgs a, const SweepArgs sw) {
+    __shared__ double red_s[8];
+    const int f = blockIdx.x, t = threadIdx.x, K = a.n_ant;
+    const double ibo_lin = (SWEEP && sw.ibo_lin_tab) ? sw.ibo_lin_tab[(sw.frame0 + (unsigned)f) / (unsigned)sw.fpp] : a.ibo_lin;
+    const double snr_lin = (SWEEP && sw.snr_lin_tab) ? sw.snr_lin_tab[(sw.frame0 + (unsigned)f) / (unsigned)sw.fpp] : a.snr_lin;
+    double a2 = 0.0;
+    if (t < K) {
+        const double dx = a.tx_pos[t * 3 + 0] - a.rx_pos[f * 3 + 0], dy = a.tx_pos[t * 3 + 1] - a.rx_pos[f * 3 + 1],
+                     dz = a.tx_pos[t * 3 + 2] - a.rx_pos[f * 3 + 2];
+        // the amplitude the channel kernel uses (rounded to float there)
+        const double amp = (double)(float)(a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846) / sqrt(dx * dx + dy * dy + dz * dz));
+        a2 = amp * amp;
+    }
+    const double A = block_sum_256(a2, red_s, t);
+    double al_a2 = 0.0;
+    if (t < K) {  // mp_model.py:315-317 + modulation.py:178-189 with vk_pow[k] = N_sc a_k^2 / A
+        const double g2 = ibo_lin * A / (a2 * (double)K);
+        const double g = sqrt(g2);
+        const double al = 1.0 - exp(-g2) + (1.7724538509055160273 * g * 0.5) * erfc(g);
+        if (a.alpha_out) a.alpha_out[(size_t)f * K + t] = (float)al;
+        al_a2 = al * a2;
+    }
+    const double S1 = block_sum_256(al_a2, red_s, t);
+    const double rA = sqrt(A);
+    double s_f = 0.0;
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        const int p = jp * 256 + t;
+        const double fr = a.freq_slot[p];
+        s_f += 1.0 / (fr * fr);
+        a.sscale[(size_t)f * N_SC + p] = (float)(fr / (64.0 * rA));
+        a.agc_inv[(size_t)f * N_SC + p] = make_float2((float)(fr * rA / (64.0 * S1)), 0.f);
+        a.hkvk_inv[(size_t)f * N_SC + p] = make_float2((float)(fr / rA), 0.f);
+    }
+    s_f = block_sum_256(s_f, red_s, t);
+    if (t == 0) {
+        const double avg = a.avg_sample_power / (double)K;   // antenna_array.py:328-341: mean |v|^2 = 1 / K
+        FrameScalars sc;
+        const double p0_tx = (a.pa_kind == PA_TOI) ? (1.0 / ibo_lin) / avg : ibo_lin * avg;
+        const double p0_cnc = (a.pa_kind == PA_TOI) ? (1.0 / ibo_lin) / a.avg_sample_power : ibo_lin * a.avg_sample_power;
+        sc.pa_p0_tx = (float)p0_tx;
+        sc.pa_p0_loop = (float)(a.is_mcnc ? p0_tx : p0_cnc);
+        const double s_agc = S1 * S1 / A * s_f, s_hv = A * s_f;
+        sc.noise_sigma = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_agc / N_SC) / snr_lin));
+        sc.noise_sigma_clean = (float)(0.5 * sqrt(2.0 * a.avg_symbol_power * (s_hv / N_SC) / snr_lin));
+        a.scal[f] = sc;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // k_clean_frame: the "no distortion" loop body (mp_model.py:158-173).  FFT(IFFT(x)) == x, so it is
 // precode -> channel -> noise -> / sum_k h_k v_k -> slice -> count.  One CTA per frame.
 // ---------------------------------------------------------------------------------------------

@@ -208,6 +208,9 @@ class Link():
             rx_bits_lst = self.my_cnc_rx.receive(n_iters_lst=iters[use], in_sig_fd=sig)
             order = np.argsort(iters[use], kind="stable")  # receive() returns ascending iteration order
             slots = (np.nonzero(use)[0] + res_idx)[order]
+            log = getattr(self, "frame_log", None)  # a list: per-frame decisions are recorded there (parity tests)
+            if log is not None:
+                log.append(dict(iters=np.sort(iters[use]), bits=[np.asarray(b) for b in rx_bits_lst], tx_bits=np.asarray(tx_bits)))
             for slot, rx_bits in zip(slots, rx_bits_lst):
                 err_arr[slot] += utilities.count_mismatched_bits(tx_bits, rx_bits)
                 bits_arr[slot] += self.n_bits_per_ofdm_sym
@@ -353,8 +356,9 @@ class Link():
                 inj, gens, states = ({} if reroll_chan else self._fixed_channel(n, "")), None, None
             else:
                 inj, gens, states = self._draw_batch(n, reroll_chan, "")
+            log = getattr(self, "frame_log", None)  # a list: per-frame decisions are recorded there (parity tests)
             out = eng.simulate(n, n_iter, snr, seed=seed, frame_id0=(1 << 40) + frame_id, csi_eps=eps, inject=inj,
-                               dumps=("err_per_frame",), noise_unit=not philox)
+                               dumps=("err_per_frame", "det") if log is not None else ("err_per_frame",), noise_unit=not philox)
             frame_id += n
             epf = out["err_per_frame"]
             used = 0
@@ -366,6 +370,8 @@ class Link():
                     if iters[j] <= n_iter:
                         err_arr[res_idx + j] += int(epf[f, iters[j]])
                         bits_arr[res_idx + j] += B
+                if log is not None:
+                    log.append(dict(det=np.array(out["det"][f]), err=np.array(epf[f]), n_iter=n_iter))
                 used += 1
             self._rewind(gens, states, used, n)
 

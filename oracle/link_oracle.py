@@ -583,37 +583,43 @@ def mu_realisation(cfg: LinkConfig, h_list, precoding="mrt"):
 
 
 def mu_frame(cfg: LinkConfig, h_list, tx_idx, noise_fd, n_iter_max, precoding="mrt", loop_single_user=False, real=None,
-             receiver=None):
+             receiver=None, rx_eq_in=None):
     """One two-user frame (script :624-642): one array transmission carrying both users, per user propagate over its
     channel, add noise (noise_fd [U, n_fft], already scaled; None = noise free), AGC, McncMuReceiver.receive
     (corrector.py:404-446) or - loop_single_user - a single-user McncReceiver on the user's own channel (:563-572).
     receiver: "mcnc_mu" (default) | "mcnc_su" (= loop_single_user) | "cnc" (single-user CncReceiver of
     main_multiuser_cnc_ber_vs_ebn0.py:124,600) | "cnc_mu" (CncMuReceiver with the other user's symbols, corrector.py:288-345).
-    Returns dict(rx_eq [U,N_sc], det [U, n_iter_max+1, N_sc], err [U, n_iter_max+1])."""
+    rx_eq_in [U, N_sc]: receiver-only use, the equalised signal is given instead of being computed.
+    Returns dict(rx_eq [U,N_sc], det [U, n_iter_max+1, N_sc], err [U, n_iter_max+1], corr [U, n_iter_max+1, N_sc] = the
+    slicer inputs, used by the parity tests for the decision margins)."""
     receiver = receiver or ("mcnc_su" if loop_single_user else "mcnc_mu")
     real = real or mu_realisation(cfg, h_list, precoding)
     tx_idx = np.asarray(tx_idx)
     x = array_transmit(cfg, tx_idx, real["v"], real["pa"])
     n_usr = len(h_list)
-    rx_eq, det, err = [], [], []
+    rx_eq, det, err, corr = [], [], [], []
     for u in range(n_usr):
-        rx = np.sum(x * h_list[u], axis=0)
-        if noise_fd is not None:
-            rx = rx + noise_fd[u]
-        y = rx[cfg.bins] / real["agc"][u]
+        if rx_eq_in is not None:
+            y = np.asarray(rx_eq_in[u])
+        else:
+            rx = np.sum(x * h_list[u], axis=0)
+            if noise_fd is not None:
+                rx = rx + noise_fd[u]
+            y = rx[cfg.bins] / real["agc"][u]
+        tr = {}
         if receiver in ("cnc", "cnc_mu"):
             alpha = float(calc_alpha(cfg.ibo_db)) if cfg.pa_kind in (PA_SOFT_LIMITER, PA_RAPP) else 1.0
             other = cfg.constellation[tx_idx[1 - u]] if receiver == "cnc_mu" else None
-            d = cnc_receive(cfg, y, cnc_pa_params(cfg), alpha, n_iter_max, other_usr_symbols=other)
+            d = cnc_receive(cfg, y, cnc_pa_params(cfg), alpha, n_iter_max, other_usr_symbols=other, trace=tr)
         elif receiver == "mcnc_su":
             su = make_realisation(cfg, h_list[u])
-            d = mcnc_receive(cfg, y, su.h_loop, su.v, su.pa, su.ak_hk_vk_agc, n_iter_max)
+            d = mcnc_receive(cfg, y, su.h_loop, su.v, su.pa, su.ak_hk_vk_agc, n_iter_max, trace=tr)
         else:
             d = mcnc_receive(cfg, y, h_list[u], real["v"], real["pa"], real["agc"][u], n_iter_max,
-                             other_usr_idx=tx_idx[1 - u], usr_idx=u)
-        rx_eq.append(y); det.append(d)
+                             other_usr_idx=tx_idx[1 - u], usr_idx=u, trace=tr)
+        rx_eq.append(y); det.append(d); corr.append(np.stack(tr["corr"]))
         err.append(count_bit_errors(tx_idx[u], d))
-    return dict(rx_eq=np.stack(rx_eq), det=np.stack(det), err=np.array(err, dtype=np.int64))
+    return dict(rx_eq=np.stack(rx_eq), det=np.stack(det), err=np.array(err, dtype=np.int64), corr=np.stack(corr))
 
 
 def frame_clean(cfg: LinkConfig, real: Realisation, tx_idx, noise_fd):

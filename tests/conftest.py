@@ -28,3 +28,12 @@ def rel_l2(a, b):
     a = np.asarray(a)
     b = np.asarray(b)
     return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """decision-flip tallies of the GPU parity tests -> $MMIMO_MARGIN_LOG (tests/parity_util.py)"""
+    try:
+        import parity_util
+        parity_util.dump_stats()
+    except Exception:
+        pass

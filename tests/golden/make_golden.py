@@ -66,8 +66,11 @@ def make_channel(kind, my_array, my_rx):
 
 
 def golden_link(name, n_ant, chan_kind, ibo, ebn0, n_frames, iters, seeds, is_mcnc=True, incl_clean=False,
-                csi_eps=None, n_fft=4096, n_sc=2048, constel=64, pa="softlim"):
-    """mp_model.Link.simulate driven exactly like main_mp_miso_mcnc_ber_vs_ebn0.py:101-134 (one worker)."""
+                csi_eps=None, n_fft=4096, n_sc=2048, constel=64, pa="softlim", full_frames=None):
+    """mp_model.Link.simulate driven exactly like main_mp_miso_mcnc_ber_vs_ebn0.py:101-134 (one worker).
+    full_frames: many-frame cases keep the bulky float64 arrays (noise, channel row, AGC) for the first `full_frames`
+    frames only and the equalised signal as complex64; decisions, error counters, positions and PA powers of ALL
+    frames are stored (the oracle regenerates everything else from the seeds)."""
     my_mod, my_dist, my_tx, my_rx, my_array = build_objects(n_ant, constel, n_fft, n_sc, 128 if n_fft >= 1024 else 16,
                                                             pa=pa, ibo=0.0)
     ch = make_channel(chan_kind, my_array, my_rx)
@@ -137,6 +140,12 @@ def golden_link(name, n_ant, chan_kind, ibo, ebn0, n_frames, iters, seeds, is_mc
     )
     if rec["pos"]:
         out["pos"] = np.array(rec["pos"], dtype=np.float64)
+    if full_frames is not None:
+        for k in ("noise_sc", "h_true_row0", "agc_sc"):
+            out[k] = out[k][:n_clean + full_frames] if k == "noise_sc" else out[k][:full_frames]
+        out["rx_eq_sc"] = out["rx_eq_sc"].astype(np.complex64)
+        out["det"] = out["det"].astype(np.uint8 if constel <= 256 else np.uint16)
+        out["tx_idx"] = out["tx_idx"].astype(np.uint8 if constel <= 256 else np.uint16)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
     print(name, "err", list(e), "bits", list(b))
 
