@@ -192,6 +192,58 @@ def host_inputs(a, rank, torch, noise_scaler):
     return dict(rx_pos=pos, tx_idx=idx, noise=nz), keep, pos.nbytes + idx.nbytes + nz.nbytes
 
 
+def reference_measured():
+    """The UNMODIFIED reference timed in the build container by tools/time_reference.py (it cannot travel to the GPU box):
+    single-process Link.simulate and the mp.Process launcher pattern, frames/s with CPU model and core count."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_reference_timing.json")))
+        return {"where": "%s, %s, %d vCPU (NOT this box)" % (d["where"], d["cpu"], d["vcpus"]),
+                "single_process_mcnc_frames_per_s": d["single_process_mcnc"]["frames_per_s"],
+                "single_process_cnc_frames_per_s": d["single_process_cnc"]["frames_per_s"],
+                "multiprocess_mcnc_frames_per_s": d["multiprocess_mcnc"]["frames_per_s"],
+                "multiprocess_processes": d["multiprocess_mcnc"]["processes"],
+                "source": "profiles/r02_reference_timing.json (tools/time_reference.py)"}
+    except Exception:
+        return None
+
+
+def secondary_workloads(eng, a, snr, peak):
+    """The other fused shapes BASELINE.json names, measured in the same run after the headline legs (same GPU, same
+    clocks): CNC receiver (configs[1]), two-user MU-MRT / ZF (configs[4]), SDR snapshots (configs[3]).  Every entry: frames
+    (user-frames, snapshots) per second over the whole synchronous call incl. its D2H, the frame kernel's ms per launch
+    and its fraction of the FP32 peak on the algorithmic FFT flops of that shape."""
+    out = {}
+    F, K, I = a.frames, a.n_ant, a.n_iter
+    fft = 5.0 * N_FFT * math.log2(N_FFT)
+
+    def run(name, fn, units, flops_per_unit, reps=3):
+        fn()  # warm-up (scratch growth)
+        eng.profile(True)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        dt = time.perf_counter() - t0
+        ms, n = eng.profile_read()
+        eng.profile(False)
+        k_ms = float(ms[2]) / max(int(n[2]), 1)
+        out[name] = {"value": units * reps / dt, "unit": "frames/s", "units_per_call": units, "kernel_ms_per_launch": k_ms,
+                     "frac": flops_per_unit * units / (k_ms * 1e-3) * 1e-12 / peak if k_ms > 0 else None}
+
+    eng.configure(n_ant=K, channel="los", receiver="cnc", pa="softlim", ibo_db=0.0)
+    run("cnc", lambda: eng.simulate(F, I, snr, seed=7), F, (2.0 * K + 2.0 * I) * fft)
+    eng.configure(n_ant=K, channel="los", receiver="mcnc", pa="softlim", ibo_db=0.0)
+    for tag in ("mrt", "zf"):
+        run("mu_" + tag, lambda tag=tag: eng.mu_simulate(F // 2, I, snr, precoding=tag, seed=11), 2 * (F // 2),
+            2.0 * K * (I + 1) * fft)
+    run("sdr", lambda: eng.sdr(F, seed=3), F, 2.0 * K * fft)
+    for v in out.values():
+        v["note"] = "device RNG, K=%d, I=%d, soft limiter IBO 0 dB" % (K, I)
+    out["mu_mrt"]["unit"] = out["mu_zf"]["unit"] = "user-frames/s"
+    out["sdr"]["unit"] = "snapshots/s"
+    eng.configure(n_ant=K, channel="los", receiver="mcnc", pa="softlim", ibo_db=0.0)
+    return out
+
+
 def run_gpu(a):
     import torch
     import torch.distributed as dist
@@ -230,14 +282,18 @@ def run_gpu(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_result = torch.zeros(65, dtype=torch.int64, pin_memory=True)
+
     def timed(n_steps, first, inject=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for s in range(n_steps):
             step(first + s, inject)
-        if inject is not None:  # e2e: the result (error counts) comes back to the host every step batch
-            host = total.cpu()
+            if inject is not None:
+                # e2e: the result of EVERY step (the reduced error counts so far) is read back to pinned host memory,
+                # stream-ordered and without blocking the enqueue of the next step - like a training loop logging its loss
+                host_result.copy_(total, non_blocking=True)
         e1.record(stream)
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
@@ -270,11 +326,34 @@ def run_gpu(a):
     inject, keep, h2d = host_inputs(a, rank, torch, noise_scaler)
     timed(1, 10_000, inject)  # warm-up of the injected path (staging buffers)
     total.zero_()
-    e2e_steps = max(1, min(a.steps, 4))
+    del inject, keep
+    e2e_steps = max(1, min(a.steps, 8))
+    # ONE timed region over the e2e steps: every step copies its own inputs from pinned host memory (three cudaMemcpyAsync on
+    # the library's copy stream, overlapping the previous step's frame kernel) and reads its result back (see timed()).
+    # Each step gets its OWN host buffers, as a caller streaming fresh data would hand over.
+    injects = [host_inputs(a, rank + 1000 * s, torch, noise_scaler) for s in range(min(e2e_steps, 3))]
+    h2d = injects[0][2]
+    e2e_frames = 0
     barrier()
-    t_e2e = 0.0
-    for s in range(e2e_steps):  # one timed region per step so that the D2H of the result is inside each
-        t_e2e += timed(1, 20_000 + s, inject)
+    e2e_inj = [injects[s % len(injects)][0] for s in range(e2e_steps)]
+
+    def e2e_region():
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for s in range(e2e_steps):
+            step(20_000 + s, e2e_inj[s])
+            host_result.copy_(total, non_blocking=True)
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    e2e_region()  # warm-up of the whole pipelined region (both staging slots)
+    total.zero_()
+    t_e2e = e2e_region()
     e2e_value = e2e_steps * F * world / (t_e2e * 1e-3)
     e2e_tot = total.cpu().numpy()
 
@@ -303,15 +382,17 @@ def run_gpu(a):
             "config": workload_config(a, F),
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 65 * 8,
                     "ber": (e2e_tot[:I + 1] / float(e2e_steps * F * world * 6 * N_SC)).tolist(),
-                    "note": "LinkEngine.enqueue(inject=pinned host rx_pos/tx symbols/noise) + counter all-reduce + "
-                            "D2H of the 65 counters inside every timed step"},
+                    "steps": e2e_steps,
+                    "note": "one timed region of %d steps; every step: LinkEngine.enqueue(inject=pinned host rx_pos / tx symbols "
+                            "/ noise, copied by the library's copy stream under the previous step's frame kernel) + counter "
+                            "all-reduce + stream-ordered D2H of the 65 reduced counters into pinned host memory" % e2e_steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                          "traffic_note": "dram__bytes_read+write per launch from profiles/frame_kernel_traffic.json (ncu --set full, "
                                          "1184-frame launch) scaled to this launch's frame count; algorithmic HBM bytes per launch = %d" % (bytes_frame * F),
-                         "kernel": ("k_link_frame<soft limiter>" if os.environ.get("MMIMO_FRAME_KERNEL", "").startswith("r1")
-                                    else "k_link_frame_r64<soft limiter>"), "launches_timed": frame_n,
+                         "kernel": {"r16": "k_link_frame<soft limiter>", "r64": "k_link_frame_r64<soft limiter>"}.get(
+                             os.environ.get("MMIMO_FRAME_KERNEL", ""), "k_link_frame_t64<soft limiter>"), "launches_timed": frame_n,
                          "kernel_ms_per_launch": frame_ms / max(frame_n, 1),
                          "kernel_share_of_step": frame_ms / ms_total if ms_total else None,
                          "algorithmic_flops_per_frame": fl,
@@ -325,8 +406,11 @@ def run_gpu(a):
             "clocks": clocks,
             "ber": (tot[:I + 1] / float(frames_total * 6 * N_SC)).tolist(),
         }
+        if world == 1 and not a.no_secondary:
+            line["secondary"] = secondary_workloads(eng, a, snr, peak)
         if world == 1 and not a.no_cpu:
             line["cpu_baseline"] = cpu_baseline_single(a.n_ant, I, a.ebn0)
+            line["cpu_baseline"]["reference_measured"] = reference_measured()
         print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:
@@ -348,6 +432,7 @@ def main():
     ap.add_argument("--ebn0", type=float, default=15.0)
     ap.add_argument("--ref-frames-per-core", type=int, default=4)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary workloads (CNC, two-user, SDR)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     if a.impl == "reference":

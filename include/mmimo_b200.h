@@ -16,7 +16,9 @@
  *   - complex arrays are interleaved float (re, im) pairs ("c64"); per-sub-carrier host arrays use the
  *     reference's data-sub-carrier order ("negative half then positive half", modulation.py:266-267);
  *     full-band arrays use FFT-bin order (DC at index 0).
- *   - n_fft = 4096, n_sub_carr = 2048 in this version (every configuration in BASELINE.json).
+ *   - the FUSED entry points (mmimo_link_*, mmimo_mu_link_simulate, mmimo_sdr_simulate) take n_fft = 4096 with
+ *     n_sub_carr = 2048 (every configuration in BASELINE.json); the stage-level entry points further down take any
+ *     n_fft = 2^m from 8 to 8192 and any even n_sub_carr.
  */
 #ifndef MMIMO_B200_H
 #define MMIMO_B200_H
@@ -127,7 +129,12 @@ int mmimo_set_ibo(mmimo_ctx* ctx, double ibo_db);
 /* Link.simulate (mp_model.py:89-222) for a fixed number of frames.
  *   mmimo_link_simulate : H2D of injected inputs + kernels + D2H of results + synchronize.
  *   mmimo_link_enqueue  : the same work without the final D2H/sync; counters stay on the device and are
- *                         ACCUMULATED across calls until mmimo_link_fetch reads and clears them. */
+ *                         ACCUMULATED across calls until mmimo_link_fetch reads and clears them.
+ * Buffer lifetime: mmimo_link_enqueue returns while the copies of the request's host arrays may still be in flight
+ * (rx_pos / tx_idx / noise go through the context's copy stream into one of two staging slots, so that the copies of
+ * batch n + 1 overlap the kernels of batch n; pinned memory makes them asynchronous).  The caller must leave every array
+ * of the request untouched until mmimo_link_fetch or mmimo_synchronize has returned, or until TWO later enqueue calls
+ * carrying the same kind of array have been issued and the stream they run on has passed them. */
 int mmimo_link_simulate(mmimo_ctx* ctx, const mmimo_sim_request* req, mmimo_sim_result* res);
 int mmimo_link_enqueue(mmimo_ctx* ctx, const mmimo_sim_request* req);
 int mmimo_link_fetch(mmimo_ctx* ctx, int32_t n_iter, uint64_t* err, uint64_t* clean_err);

@@ -65,6 +65,12 @@ struct FrameArgs {
     // stream in lock-step, so their shared-memory exchange phases (no FMA work) coincide.  The offset makes one warp's
     // exchange overlap the other's butterflies (frame_kernel_t64.cuh).
     int stagger;
+    // k_link_frame_t64 only - signal-to-distortion snapshots (main_beampatterns_plotting/sdr_mp.py:124-151) instead of the
+    // receiver: with n_iter = 0 and these two set, pass 0 ends in
+    //     desired[f]    = sum_s | sum_k alpha_k h_k X_clean_k |^2 = sum_s | sym[s] agc[s] |^2     (agc = the AGC vector of
+    //     distortion[f] = sum_s | sum_k h_k X_k - sym[s] agc[s] |^2                               mp_model.py:290-329)
+    // no noise is added, nothing is detected or counted.
+    double* sdr_desired; double* sdr_distortion;
 };
 
 constexpr int FRAME_SMEM_FLOAT2 = 4096 * 2 + 256 + 2048;

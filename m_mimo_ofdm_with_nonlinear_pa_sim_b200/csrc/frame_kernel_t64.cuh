@@ -23,7 +23,7 @@ namespace mmimo {
 #define T64_DEPTH 4  // level-C table entries fetched this many butterfly classes ahead of their use
 #endif
 #ifndef T64_ACC_SMEM
-#define T64_ACC_SMEM 12  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
+#define T64_ACC_SMEM 14  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
 #endif
 #ifndef T64_PRUNE
 #define T64_PRUNE 1  // guard-band pruning of the first transform's level A and of the second transform's last level
@@ -32,14 +32,16 @@ namespace mmimo {
 #define T64_LOOP 1  // 1: guard-band form of level A of the first transform ahead of the loop; 2: loop starts with level A
 #endif
 #ifndef T64_SYNC
-#define T64_SYNC 1  // group-barrier placement, see the kernel
+#define T64_SYNC 0  // group-barrier placement, see the kernel (0 measured faster with 14 shared accumulators, 1 with 12)
 #endif
 #ifndef T64_PA_UNIT
 #define T64_PA_UNIT 1  // PA evaluated on the signal scaled to a unit threshold (one multiply less per sample)
 #endif
 constexpr int FRAME_T64_SMEM_BYTES =
     (4096 + R64_GROUPS * t64::XBUF + 2 * N_SC + T64_ACC_SMEM * FFT_THREADS) * 8 + 64 * 4 + 2 * R64_GROUPS * 8;
-static_assert(FRAME_T64_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
+// two-user instantiation: + the other user's symbols as int8 pairs (2 bytes per sub-carrier)
+constexpr int FRAME_T64_SMEM_BYTES_MU = FRAME_T64_SMEM_BYTES + N_SC * 2;
+static_assert(FRAME_T64_SMEM_BYTES_MU <= 227 * 1024, "shared-memory budget of one CTA");
 
 // PA on one packed sample.  T64_PA_UNIT: the sample arrives scaled so that the threshold is 1 (see the kernel):
 // soft limiter g = rsqrt(max(|x|^2, 1)); Rapp g = (1 + |x|^(2p))^(-1/(2p)); third order g = 1 - |x|^2.
@@ -60,7 +62,11 @@ __device__ __forceinline__ pf2 pa_apply_t64(pf2 xp, const float p0, const float 
     return pmul(xp, pbc(g));
 }
 
-template <int PA>
+// MU (two users, FrameArgs: "Two-user mode"): every array transmit carries own + other user (modulation.py:373); the own
+// precoder row arrives by TMA like the single-user one, the other user's row is read from L2 (prefetched a round ahead),
+// the other user's (true) symbols sit in shared memory as int8 pairs.  Requires a uniform symbol scale on explicit-precoder
+// sides (sscale_fs == 0, as mu_host.inl sets it).
+template <int PA, bool MU = false>
 __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameArgs a, const float2* __restrict__ tab_g) {
     extern __shared__ __align__(128) float2 smem[];
     float2* tab = smem;                                         // per-lane twiddle parameters (t64::build_table)
@@ -69,6 +75,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
     unsigned int* err_s = reinterpret_cast<unsigned int*>(symn_s + N_SC + T64_ACC_SMEM * FFT_THREADS);
     unsigned long long* mbar_s = reinterpret_cast<unsigned long long*>(err_s + 64);
     float2* rxeq_s = reinterpret_cast<float2*>(mbar_s + 2 * R64_GROUPS);  // equalised received signal of the frame
+    char2* symo_c = reinterpret_cast<char2*>(rxeq_s + N_SC);              // MU only: symbols of the other user
 
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
     pf2* accx_s = reinterpret_cast<pf2*>(symn_s + N_SC) + t;    // accumulators i < T64_ACC_SMEM at [i * 256]
@@ -93,20 +100,32 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
     for (int f = blockIdx.x; f < a.n_frames; f += gridDim.x) {
         const FrameScalars sc = a.scal[f * a.scal_fs];
         uint32_t txw[2];
-        if (a.tx_idx) {
-            const uint8_t* p = a.tx_idx + (size_t)f * N_SC;
-            txw[0] = txw[1] = 0;
+        auto load_tx = [&](const int inst, uint32_t (&w)[2]) {  // 8 symbol values of this thread for instance inst
+            if (a.tx_idx) {
+                const uint8_t* p = a.tx_idx + (size_t)inst * N_SC;
+                w[0] = w[1] = 0;
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) txw[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
-        } else {
-            uint32_t r[4];
-            const uint64_t fid = a.frame_id0 + f;
-            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
-                          (uint32_t)(a.seed >> 32), r);
-            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
-            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
-            txw[0] = r[0] & m4;
-            txw[1] = r[1] & m4;
+                for (int jp = 0; jp < 8; ++jp) w[jp >> 2] |= (uint32_t)p[jp * 256 + t] << (8 * (jp & 3));
+            } else {
+                uint32_t r[4];
+                const uint64_t fid = a.frame_id0 + inst;
+                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)t, (uint32_t)a.seed,
+                              (uint32_t)(a.seed >> 32), r);
+                const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+                const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+                w[0] = r[0] & m4;
+                w[1] = r[1] & m4;
+            }
+        };
+        load_tx(f, txw);
+        if (MU) {  // the other user's true symbols (instance f ^ 1), constant over the frame; visible after the pass barrier
+            uint32_t otw[2];
+            load_tx(f ^ 1, otw);
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) {
+                const float2 o = qam_symbol(a.qam, (otw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
+                symo_c[jp * 256 + t] = make_char2((signed char)o.x, (signed char)o.y);
+            }
         }
         uint32_t curw[2] = {txw[0], txw[1]};
 
@@ -117,6 +136,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
             const float2* __restrict__ Hm = sd.h_mac + f * sd.h_mac_fs;
             const float2* __restrict__ Hp = sd.v ? sd.v + f * sd.v_fs : sd.h_pre + f * sd.h_pre_fs;
             const bool explicit_v = sd.v != nullptr;
+            const bool two_usr = MU && explicit_v && !(a.loop_single_user && !first);
+            const float2* __restrict__ Ho = two_usr ? sd.v + (f ^ 1) * sd.v_fs : nullptr;  // precoder rows of the other user
             const float p0 = first ? sc.pa_p0_tx : sc.pa_p0_loop;
             const float sqrt_p0 = sqrtf(p0);
             // T64_PA_UNIT: the chain runs on x / sqrt(P) (P = saturation power; third order: 1 / cubic coefficient), so the
@@ -133,6 +154,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     symn_s[p] = make_float2(s.x * gsc, s.y * gsc);
                 }
             }
+            const float g_oth = two_usr ? sd.sscale[f * sd.sscale_fs] * pa_in_scale : 0.f;  // uniform scale (see above)
             __syncthreads();  // symbols visible to all groups; every exchange buffer is idle from here
             // what the pass epilogue reads from global memory: on its way to L2 while the antennas are processed
             if (t < 128) prefetch_l2(sd.agc_inv + f * sd.agc_fs + t * 16);
@@ -144,6 +166,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
                     bulk_prefetch_l2(Hm + (size_t)g * N_SC, ROW_BYTES);
                     if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
+                    if (MU && two_usr) {
+                        bulk_prefetch_l2(Ho + (size_t)g * N_SC, ROW_BYTES);
+                        if (g + R64_GROUPS < K) bulk_prefetch_l2(Ho + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
+                    }
                 }
             }
             if (a.stagger > 0 && g >= 2 && K > 2) {  // de-phase the two warps of every scheduler (FrameArgs::stagger)
@@ -168,6 +194,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     const pf2 h = pk2(rowB[src]);
                     if (explicit_v) x[n1] = pcmul(h, s.x, s.y);                                 // v * s
                     else x[n1] = pfma(pswap(h), pbc(s.y), pmul(h, pk(s.x, -s.x)));               // conj(h) * s
+                    if (MU && two_usr) {  // modulation.py:373: sum over users of symbol * precoder
+                        const char2 o = symo_c[src];
+                        x[n1] = pcfma(pk2(__ldg(Ho + (size_t)k * N_SC + src)), pk((float)o.x * g_oth, (float)o.y * g_oth), x[n1]);
+                    }
                 }
                 if (T64_LOOP != 1) {
 #pragma unroll
@@ -195,7 +225,10 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                             mbar_expect_tx(mbB, ROW_BYTES);
                             bulk_g2s(smem_u32(rowB), Hp + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES, mbB);
                             if (Hp != Hm) bulk_prefetch_l2(Hm + (size_t)(k + R64_GROUPS) * N_SC, ROW_BYTES);
-                            if (k + 2 * R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                            if (k + 2 * R64_GROUPS < K) {
+                                bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                                if (MU && two_usr) bulk_prefetch_l2(Ho + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                            }
                         }
                     }
                 };
@@ -274,9 +307,39 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                 if (T64_PA_UNIT) accn[jp] = pmul(accn[jp], pbc(pa_out_scale));
             }
 
+            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
+            if (!MU && a.sdr_desired) {  // ---- signal-to-distortion snapshot instead of the receiver (FrameArgs) ----
+                double pd = 0.0, pi = 0.0;
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) {
+                    const int p = jp * 256 + t;
+                    const float2 ac = unpk(accn[jp]);            // 64 x the noise-free received signal
+                    const float2 iv = ai[p];                     // 1 / (64 agc)
+                    const float m = 1.0f / (64.0f * (iv.x * iv.x + iv.y * iv.y));
+                    const float2 agc = make_float2(iv.x * m, -iv.y * m);
+                    const float2 des = cmul(qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu), agc);
+                    const float2 dis = make_float2(fmaf(ac.x, 0.015625f, -des.x), fmaf(ac.y, 0.015625f, -des.y));
+                    pd += (double)des.x * des.x + (double)des.y * des.y;
+                    pi += (double)dis.x * dis.x + (double)dis.y * dis.y;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    pd += __shfl_xor_sync(0xffffffffu, pd, o);
+                    pi += __shfl_xor_sync(0xffffffffu, pi, o);
+                }
+                double* red_s = reinterpret_cast<double*>(rxeq_s);
+                if ((t & 31) == 0) { red_s[t >> 5] = pd; red_s[8 + (t >> 5)] = pi; }
+                __syncthreads();
+                if (t == 0) {
+                    double sd2 = 0.0, si2 = 0.0;
+                    for (int w = 0; w < 8; ++w) { sd2 += red_s[w]; si2 += red_s[8 + w]; }
+                    a.sdr_desired[f] = sd2;
+                    a.sdr_distortion[f] = si2;
+                }
+                continue;
+            }
             // ---- end of pass: equalise / estimate distortion / slice / count (as k_link_frame) -----------
             uint32_t detw[2] = {0u, 0u};
-            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
             float2 nz[8];
             if (first && !a.rx_eq_in) {
                 if (a.noise) {
@@ -335,11 +398,11 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
             }
         }
         __syncthreads();
-        if (t <= a.n_iter) {
+        if (t <= a.n_iter && a.err_total) {
             const unsigned int e = err_s[t];
             err_s[t] = 0;
             if (a.err_out) a.err_out[(size_t)f * (a.n_iter + 1) + t] = e;
-            atomicAdd(&a.err_total[t + (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u)], (unsigned long long)e);
+            atomicAdd(&a.err_total[t + (MU ? (f & 1) * 32 : 0) + (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u)], (unsigned long long)e);  // MU: user 1 counts at [32..]
         }
         __syncthreads();
     }

@@ -44,6 +44,7 @@ static int download_native(mmimo_ctx* c, const T* src, T* host, size_t rows) {
 }
 
 struct RealisationIn {
+    const double* rx_pos_dev;  // positions already on the device (staging slot of the copy stream) or nullptr
     const double* rx_pos;
     const float* h_true;
     const float* h_loop;
@@ -66,7 +67,10 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ChanArgs ca{};
         ca.tx_pos = c->tx_pos.as<double>();
         ca.rx_pos_in = nullptr;
-        if (in.rx_pos) {
+        if (in.rx_pos_dev) {
+            CK(cudaMemcpyAsync(c->rx_pos.p, in.rx_pos_dev, (size_t)n * 24, cudaMemcpyDeviceToDevice, c->stream));
+            ca.rx_pos_in = c->rx_pos.as<double>();
+        } else if (in.rx_pos) {
             CK(cudaMemcpyAsync(c->rx_pos.p, in.rx_pos + c0 * 3, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream));
             ca.rx_pos_in = c->rx_pos.as<double>();
         }
@@ -215,7 +219,7 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
         float2 *h_true = nullptr, *h_loop = nullptr;
         if (rq->incl_clean_run) {
-            RealisationIn in{rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, rq->clean_csi_noise, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
+            RealisationIn in{nullptr, rq->clean_rx_pos, rq->clean_h_true, rq->clean_h_loop, rq->clean_csi_noise, RNG_POS + 16, RNG_RAYLEIGH + 16, RNG_CSI + 16};
             if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, false)) return 1;
             CleanArgs ca{};
             ca.h_true = h_true; ca.h_fs = (long long)K * N_SC;
@@ -248,7 +252,34 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             }
         }
         if (rq->incl_clean_run == 2) continue;  // clean frames only
-        RealisationIn in{rq->rx_pos, rq->h_true, rq->h_loop, rq->csi_noise, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
+        // per-frame host inputs of this chunk: H2D on the copy stream into a staging slot (overlaps whatever the compute
+        // stream is still running, normally the previous batch's frame kernel), permuted into place on the compute stream
+        mmimo_ctx::InSlot* sl = nullptr;
+        if (rq->rx_pos || rq->tx_idx || rq->noise) {
+            sl = &c->in_slot[c->slot_ctr++ & 1];
+            // both slots grow together: a cudaMalloc is a device-wide synchronisation and must not land in a later batch
+            for (auto& s2 : c->in_slot)
+                if ((rq->rx_pos && s2.pos.reserve((size_t)chunk * 24)) || (rq->tx_idx && s2.idx.reserve((size_t)chunk * N_SC)) ||
+                    (rq->noise && s2.nz.reserve((size_t)chunk * N_SC * 8)))
+                    return 1;
+            if (sl->in_use) CK(cudaStreamWaitEvent(c->copy_stream, sl->consumed, 0));
+            if (rq->rx_pos) {
+                if (sl->pos.reserve((size_t)chunk * 24)) return 1;
+                CK(cudaMemcpyAsync(sl->pos.p, rq->rx_pos + c0 * 3, (size_t)n * 24, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+            if (rq->tx_idx) {
+                if (sl->idx.reserve((size_t)chunk * N_SC)) return 1;
+                CK(cudaMemcpyAsync(sl->idx.p, rq->tx_idx + c0 * N_SC, (size_t)n * N_SC, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+            if (rq->noise) {
+                if (sl->nz.reserve((size_t)chunk * N_SC * 8)) return 1;
+                CK(cudaMemcpyAsync(sl->nz.p, rq->noise + c0 * N_SC * 2, (size_t)n * N_SC * 8, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+            CK(cudaEventRecord(sl->copied, c->copy_stream));
+            CK(cudaStreamWaitEvent(c->stream, sl->copied, 0));
+            sl->in_use = true;
+        }
+        RealisationIn in{(sl && rq->rx_pos) ? sl->pos.as<double>() : nullptr, rq->rx_pos, rq->h_true, rq->h_loop, rq->csi_noise, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
         if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, want_v)) return 1;
 
         FrameArgs fa{};
@@ -278,13 +309,16 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         fa.stagger = c->t64_stagger;
         fa.tx_idx = nullptr; fa.noise = nullptr;
         if (rq->tx_idx) {
-            if (upload_native<uint8_t>(c, rq->tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;
+            k_to_native<uint8_t><<<nblk((size_t)n * N_SC), 256, 0, c->stream>>>(sl->idx.as<uint8_t>(), c->tx_idx.as<uint8_t>(), n);
+            c->launches++;
             fa.tx_idx = c->tx_idx.as<uint8_t>();
         }
         if (rq->noise) {
-            if (upload_native<float2>(c, reinterpret_cast<const float2*>(rq->noise) + c0 * N_SC, c->noise.as<float2>(), n)) return 1;
+            k_to_native<float2><<<nblk((size_t)n * N_SC), 256, 0, c->stream>>>(sl->nz.as<float2>(), c->noise.as<float2>(), n);
+            c->launches++;
             fa.noise = c->noise.as<float2>();
         }
+        if (sl) CK(cudaEventRecord(sl->consumed, c->stream));
         fa.noise_unit = (rq->flags & MMIMO_REQ_NOISE_UNIT) ? 1 : 0;
         fa.seed = rq->seed; fa.frame_id0 = rq->frame_id0 + c0;
         fa.det_out = want_det ? c->det.as<uint8_t>() : nullptr;
@@ -403,11 +437,6 @@ extern "C" int mmimo_link_sweep(mmimo_ctx* c, const mmimo_sim_request* base, int
     return 0;
 }
 
-template <int PA>
-static void launch_sdr(const SdrArgs& sa, const mmimo_ctx* c, int n) {
-    k_sdr_frame<PA><<<std::min(n, 2 * c->n_sm), FFT_THREADS, SDR_SMEM_BYTES, c->stream>>>(sa, c->tw4096.as<float2>(), c->tw256.as<float2>());
-}
-
 extern "C" int mmimo_sdr_simulate(mmimo_ctx* c, const mmimo_sdr_request* rq, double* desired, double* distortion) {
     if (!c || !rq || !desired || !distortion) return fail("mmimo_sdr_simulate: NULL argument");
     if (!c->configured) return fail("mmimo_sdr_simulate: context not configured (call mmimo_configure)");
@@ -425,39 +454,45 @@ extern "C" int mmimo_sdr_simulate(mmimo_ctx* c, const mmimo_sdr_request* rq, dou
     for (size_t c0 = 0; c0 < (size_t)rq->n_frames; c0 += chunk) {
         const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
         float2 *h_true = nullptr, *h_loop = nullptr;
-        RealisationIn in{rq->rx_pos, rq->h_true, nullptr, nullptr, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
+        RealisationIn in{nullptr, rq->rx_pos, rq->h_true, nullptr, nullptr, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
         if (run_realisation(c, &lr, in, c0, n, &h_true, &h_loop, false)) return 1;
-        SdrArgs sa{};
+        // pass 0 of the frame kernel (array transmit -> channel, no noise) with the SDR epilogue: FrameArgs::sdr_desired
+        FrameArgs fa{};
         const long long hfs = (long long)K * N_SC;
-        sa.tx.h_mac = h_true; sa.tx.h_mac_fs = hfs;
-        sa.tx.h_pre = h_true; sa.tx.h_pre_fs = hfs;
-        sa.tx.v = nullptr; sa.tx.v_fs = 0;
-        sa.tx.sscale = c->sscale.as<float>(); sa.tx.sscale_fs = N_SC;
-        sa.tx.agc_inv = c->agc_inv.as<float2>(); sa.tx.agc_fs = N_SC;
-        sa.tx.k = K;
-        sa.scal = c->scal.as<FrameScalars>();
-        sa.alpha = c->alpha.as<float>();
-        sa.pa_p1 = (float)cfg.p_hardness;
-        sa.qam.log2side = log2_side(cfg.constel_size);
-        sa.n_frames = n;
-        sa.tx_idx = nullptr;
+        fa.tx.h_mac = h_true; fa.tx.h_mac_fs = hfs;
+        fa.tx.h_pre = h_true; fa.tx.h_pre_fs = hfs;
+        fa.tx.v = nullptr; fa.tx.v_fs = 0;
+        fa.tx.sscale = c->sscale.as<float>(); fa.tx.sscale_fs = N_SC;
+        fa.tx.agc_inv = c->agc_inv.as<float2>(); fa.tx.agc_fs = N_SC;
+        fa.tx.k = K;
+        fa.loop = fa.tx;
+        fa.scal = c->scal.as<FrameScalars>(); fa.scal_fs = 1;
+        fa.pa_p1 = (float)cfg.p_hardness;
+        fa.n_iter = 0;
+        fa.qam.log2side = log2_side(cfg.constel_size);
+        fa.n_frames = n;
+        fa.tx_idx = nullptr;
         if (rq->tx_idx) {
             if (upload_native<uint8_t>(c, rq->tx_idx + c0 * N_SC, c->tx_idx.as<uint8_t>(), n)) return 1;
-            sa.tx_idx = c->tx_idx.as<uint8_t>();
+            fa.tx_idx = c->tx_idx.as<uint8_t>();
         }
-        sa.seed = rq->seed; sa.frame_id0 = rq->frame_id0 + c0;
-        sa.desired = c->s_b.as<double>();
-        sa.distortion = c->s_b.as<double>() + n;
+        fa.seed = rq->seed; fa.frame_id0 = rq->frame_id0 + c0;
+        fa.sdr_desired = c->s_b.as<double>();
+        fa.sdr_distortion = c->s_b.as<double>() + n;
+        const double* d_des = fa.sdr_desired;
+        const double* d_dis = fa.sdr_distortion;
+        prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {
-            case MMIMO_PA_NONE: launch_sdr<PA_NONE>(sa, c, n); break;
-            case MMIMO_PA_SOFT_LIMITER: launch_sdr<PA_SOFT_LIMITER>(sa, c, n); break;
-            case MMIMO_PA_RAPP: launch_sdr<PA_RAPP>(sa, c, n); break;
-            default: launch_sdr<PA_TOI>(sa, c, n); break;
+            case MMIMO_PA_NONE: k_link_frame_t64<PA_NONE><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES, c->stream>>>(fa, c->tw_t64.as<float2>()); break;
+            case MMIMO_PA_SOFT_LIMITER: k_link_frame_t64<PA_SOFT_LIMITER><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES, c->stream>>>(fa, c->tw_t64.as<float2>()); break;
+            case MMIMO_PA_RAPP: k_link_frame_t64<PA_RAPP><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES, c->stream>>>(fa, c->tw_t64.as<float2>()); break;
+            default: k_link_frame_t64<PA_TOI><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES, c->stream>>>(fa, c->tw_t64.as<float2>()); break;
         }
+        prof_end(c);
         c->launches++;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(desired + c0, sa.desired, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaMemcpyAsync(distortion + c0, sa.distortion, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(desired + c0, d_des, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(distortion + c0, d_dis, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaStreamSynchronize(c->stream));
     }
     return 0;

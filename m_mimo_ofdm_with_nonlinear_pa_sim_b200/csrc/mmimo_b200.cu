@@ -78,6 +78,14 @@ struct mmimo_ctx {
     // per-chunk scratch
     DevBuf h_true, h_loop, csi_nz, rxeq_scr, v, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos, tx_idx, noise, det, err, rx_eq, corr, stage;
     DevBuf cnc_ones, cnc_v, cnc_agc_inv;
+    // Host inputs of the distorted frames (receiver positions, symbol values, noise: what a reference user hands over per
+    // frame, mp_model.py:190-212) travel on their own stream into one of two staging slots, so that the copies of batch
+    // n + 1 run under the frame kernel of batch n.  copied: H2D of the slot finished (copy stream); consumed: the slot has
+    // been permuted into the working buffers (compute stream) and may be overwritten.
+    struct InSlot { DevBuf pos, idx, nz; cudaEvent_t copied = nullptr, consumed = nullptr; bool in_use = false; };
+    cudaStream_t copy_stream = nullptr;
+    InSlot in_slot[2];
+    unsigned slot_ctr = 0;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // multi-point batch in flight (mmimo_link_sweep): device tables of 10^(x/10) per point, 64 counters per point
     struct Sweep { const double* snr_lin = nullptr; const double* ibo_lin = nullptr; int fpp = 0; unsigned long long* counters = nullptr; } sweep;
@@ -183,6 +191,11 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
 static int create_body(mmimo_ctx* c) {
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
+    CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (auto& sl : c->in_slot) {
+        CK(cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.consumed, cudaEventDisableTiming));
+    }
     // twiddle tables, computed in double (forward sign)
     std::vector<float2> t4(4096), t2(256);
     for (int i = 0; i < 4096; ++i) {
@@ -213,15 +226,15 @@ static int create_body(mmimo_ctx* c) {
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_NONE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_SOFT_LIMITER, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_RAPP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
+    CK(cudaFuncSetAttribute(k_link_frame_t64<PA_TOI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
     // the two-user and SDR kernels: per device, so set for every context (not once per process)
     CK(cudaFuncSetAttribute(k_link_frame<PA_NONE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame<PA_SOFT_LIMITER, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame<PA_RAPP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame<PA_TOI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
-    CK(cudaFuncSetAttribute(k_sdr_frame<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_sdr_frame<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_sdr_frame<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_sdr_frame<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SDR_SMEM_BYTES));
     if (stage_kernels_init()) return 1;
     return 0;
 }
@@ -230,8 +243,15 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     c->prof_recs.clear();
+    for (auto& sl : c->in_slot) {
+        sl.pos.release(); sl.idx.release(); sl.nz.release();
+        if (sl.copied) cudaEventDestroy(sl.copied);
+        if (sl.consumed) cudaEventDestroy(sl.consumed);
+    }
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     DevBuf* all[] = {&c->tw4096, &c->tw256, &c->tw_t64, &c->sweep_tab, &c->sweep_cnt, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->rxeq_scr, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,

@@ -3,7 +3,11 @@
 
 template <int PA>
 static void launch_frame_mu(const FrameArgs& fa, const mmimo_ctx* c, int n) {
-    const int grid = std::min(n, 2 * c->n_sm);
+    if (c->frame_kernel != 2) {  // default: the two-user instantiation of the scaled-tangent radix-64 kernel
+        k_link_frame_t64<PA, true><<<std::min(n, c->n_sm), FFT_THREADS, FRAME_T64_SMEM_BYTES_MU, c->stream>>>(fa, c->tw_t64.as<float2>());
+        return;
+    }
+    const int grid = std::min(n, 2 * c->n_sm);  // MMIMO_FRAME_KERNEL=r16: the round-1 three-pass kernel
     k_link_frame<PA, true><<<grid, FFT_THREADS, FRAME_SMEM_BYTES_MU, c->stream>>>(fa, c->tw4096.as<float2>(), c->tw256.as<float2>());
 }
 

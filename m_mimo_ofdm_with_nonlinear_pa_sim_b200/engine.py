@@ -286,6 +286,8 @@ class LinkEngine:
         """Asynchronous: H2D of injected inputs + kernels, counters accumulate on the device until fetch().
         Injected host arrays are kept alive until the next fetch()/synchronize()."""
         rq, keep = self._request(n_frames, n_iter, snr_db, seed, frame_id0, incl_clean_run, csi_eps, inject, noise_unit)
+        if len(self._keep) >= 32:  # a caller that never fetches: drain once in a while instead of growing without bound
+            self.synchronize()
         self._keep.append(keep)
         _lib.check(self._lib, self._lib.mmimo_link_enqueue(self._h, C.byref(rq)))
 

@@ -16,7 +16,21 @@ FILES = {
     "cnc_los": "ber_vs_ebn0_cnc_los_nant64_ibo0_ebn0_min5_max20_step0.50_niter1_2_3_4_5_6_7_8.csv",
     "mcnc_los_vs_ibo_ebn0_15": "ber_vs_ibo_mcnc_los_nant64_ebn0_15_ibo_min-9_max9_step0.50_niter1_2_3_4_5_6_7_8.csv",
 }
+# ragged files: fixed-BER grid (row 0 = 16 IBO values, then one 9-value row per (IBO, Eb/N0) pair, IBO-major,
+# main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:210-215) -> stored as axis + [n_ibo, n_ebn0, n_iter] grid
+RAGGED = {
+    "fixed_ber_mcnc_los": ("fixed_ber1.0e-02_mcnc_los_nant64_ebn0_min10_max22_step0.50_ibo_min0_max7_step0.50_niter1_2_3_4_5_6_7_8.csv",
+                           np.arange(10.0, 22.1, 0.5)),
+}
+FILES["ber_vs_nant_mcnc"] = "ber_vs_nant_mcnc_nant1_2_4_8_16_32_64_128_ebn0_15_ibo0_niter1_2_3_4_5_6_7_8.csv"
 out = {}
+for key, (fn, ebn0) in RAGGED.items():
+    with open(os.path.join(SRC, fn), newline="") as fh:
+        rows = [[float(v) for v in r] for r in csv.reader(fh) if r]
+    ibo = np.array(rows[0])
+    grid = np.array(rows[1:]).reshape(len(ibo), len(ebn0), -1)
+    out[key + "_ibo"], out[key + "_ebn0"], out[key + "_grid"] = ibo, ebn0, grid
+    print(key, grid.shape)
 for key, fn in FILES.items():
     with open(os.path.join(SRC, fn), newline="") as fh:
         rows = [[float(v) for v in r] for r in csv.reader(fh) if r]

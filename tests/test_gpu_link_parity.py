@@ -9,14 +9,21 @@ import pytest
 
 from conftest import load_golden, rel_l2
 from oracle import link_oracle as lo
+from parity_util import MARGIN, check_frame
 
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-5      # relative L2, complex stages
-MARGIN = 2e-4   # absolute distance to a slicer boundary below which an fp32 flip is tolerated
 
 GOLDEN_4096 = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k8_los_csi",
-               "link_k8_los_rapp"]
+               "link_k8_los_rapp",
+               # the headline shape with 32 frames and its CNC twin with 16 (tests/golden/make_golden_k64.py)
+               "link_k64_los_mcnc32", "link_k64_los_cnc16"]
+# Frames that may hit a sub-margin decision, per case.  Measured on the B200 (profiles/r02_margin_histogram.json): of 1.5 M
+# decisions compared over all cases NONE differed from the reference, although the oracle's slicer input came as close as
+# 5e-7 to a boundary; the allowance below is slack for other inputs, the rule itself (parity_util.check_frame: a differing
+# decision must sit within MARGIN of a boundary) is never relaxed.
+MAX_DIVERGED_FRACTION = 1.0 / 16
 
 
 @pytest.fixture(scope="module")
@@ -40,19 +47,7 @@ def oracle_run(cfg, snr_db, n_iter, seeds, n_frames, is_mcnc, incl_clean, csi):
                             csi_eps=csi, return_frames=True)
 
 
-def compare_decisions(det_gpu, det_ref, corr_ref, constel, iters=None):
-    """det_*: [I+1, N_sc].  Returns (n_iterations_compared_exactly, diverged?)."""
-    n_it = det_ref.shape[0]
-    for it in range(n_it):
-        mism = det_gpu[it] != det_ref[it]
-        if mism.any():
-            m = lo.detection_margin(corr_ref[it][mism], constel)
-            assert m.max() < MARGIN, "iteration %d: %d decisions differ with margin up to %.3g" % (it, mism.sum(), m.max())
-            return it, True
-    return n_it, False
-
-
-def run_case(engine, cfg, snr_db, iters, seeds, n_frames, is_mcnc, incl_clean, csi, golden=None):
+def run_case(engine, cfg, snr_db, iters, seeds, n_frames, is_mcnc, incl_clean, csi, golden=None, name=None):
     n_iter = int(np.max(iters))
     errs, bits, frames = oracle_run(cfg, snr_db, n_iter, seeds, n_frames, is_mcnc, incl_clean, csi)
     pa = {lo.PA_SOFT_LIMITER: "softlim", lo.PA_RAPP: "rapp", lo.PA_TOI: "toi"}[cfg.pa_kind]
@@ -75,23 +70,24 @@ def run_case(engine, cfg, snr_db, iters, seeds, n_frames, is_mcnc, incl_clean, c
         assert np.allclose(out["alpha"][i], real.alpha_k, rtol=1e-5)
         assert rel_l2(out["rx_eq"][i], fr["rx_eq_sc"]) < TOL
         corr_ref = fr["corr"]
-        n_ok, div = compare_decisions(out["det"][i].astype(np.int64), fr["det"], corr_ref, cfg.constel_size)
-        n_div += div
+        case = name or "fused K=%d %s %s" % (cfg.n_ant, cfg.channel, "mcnc" if is_mcnc else "cnc")
+        n_ok = check_frame(case, out["det"][i], fr["det"], corr_ref, cfg.constel_size, out["err_per_frame"][i], fr["err"])
+        n_div += n_ok < fr["det"].shape[0]
         for it in range(n_ok):
             assert rel_l2(out["corr"][i, it], corr_ref[it]) < 5 * TOL
-            assert out["err_per_frame"][i, it] == fr["err"][it]
         if golden is not None:  # the reference's own outputs
             gdet = golden["det"][i].astype(np.int64)
             sel = [k for k, itv in enumerate(iters) if itv < n_ok]
             assert np.array_equal(out["det"][i][np.asarray(iters)[sel]], gdet[sel])
             assert rel_l2(out["rx_eq"][i], golden["rx_eq_sc"][i]) < TOL
-            assert rel_l2(out["agc"][i], golden["agc_sc"][i]) < TOL
+            if i < len(golden["agc_sc"]):
+                assert rel_l2(out["agc"][i], golden["agc_sc"][i]) < TOL
     if n_div == 0:
         off = 1 if incl_clean else 0
         assert np.array_equal(out["err"].astype(np.int64), errs[off:])
         if golden is not None:
             assert np.array_equal(out["err"].astype(np.int64)[np.asarray(iters)], golden["err"].astype(np.int64)[off:])
-    assert n_div <= max(1, n_frames // 2), "too many frames hit a sub-margin decision"
+    assert n_div <= max(1, int(n_frames * MAX_DIVERGED_FRACTION)), "too many frames hit a sub-margin decision"
     return out, frames
 
 
@@ -101,7 +97,7 @@ def test_golden_link_cases(engine, name):
     cfg = cfg_from_golden(g)
     csi = float(g["csi_eps"])
     run_case(engine, cfg, float(g["snr_db"]), [int(v) for v in g["iters"]], list(g["seeds"]), int(g["n_frames"]),
-             bool(g["is_mcnc"]), bool(g["incl_clean"]), None if csi < 0 else csi, golden=g)
+             bool(g["is_mcnc"]), bool(g["incl_clean"]), None if csi < 0 else csi, golden=g, name=name)
 
 
 @pytest.mark.parametrize("constel,pa,ibo", [(4, lo.PA_SOFT_LIMITER, -3.0), (16, lo.PA_SOFT_LIMITER, 2.0),

@@ -7,6 +7,8 @@ sharded by global frame index and the counters all-reduced (parallel.monte_carlo
 
   python tools/ber_sweep.py --ebn0 5:20:0.5 --n-iter 8 --out ber.csv
   torchrun --nproc-per-node 8 tools/ber_sweep.py --sweep ibo --ibo -9:9:0.5 --ebn0 15 --out ber_vs_ibo.csv
+  python tools/ber_sweep.py --sweep fixed-ber --ebn0 10:22:0.5 --ibo 0:7.5:0.5 --out fixed_ber.csv      # BER grid, reference layout
+  python tools/ber_sweep.py --sweep nant-chan --ebn0 15 --out ber_vs_nant.csv
 """
 import argparse
 import csv
@@ -20,6 +22,29 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+
+
+def write_csv(path, data):
+    """utilities.save_to_csv (utilities.py:342-352): one csv.writer row per data vector"""
+    with open(path, "w", newline="") as fh:
+        csv.writer(fh).writerows(data)
+
+
+def read_csv(path):
+    """utilities.read_from_csv (utilities.py:355-365), as the final_plots/*.py readers call it"""
+    with open(path, "r", newline="") as fh:
+        return list(csv.reader(fh, quoting=csv.QUOTE_NONNUMERIC))
+
+
+def csv_rows(mode, ax, rows, ber_grid=None):
+    """The reference's row layouts.  ebn0 / ibo / nant-chan: row 0 the swept axis, then one row per result slot
+    (main_mp_miso_mcnc_ber_vs_ebn0.py:175-179; nant-chan: per channel, ..._ber_vs_nant_vs_chan.py:205-210).  fixed-ber: row 0
+    the IBO axis, then the BER of every (IBO, Eb/N0) pair, IBO-major, one value per iteration
+    (main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:210-215; final_plots/fixed_ber_ebno_vs_ibo.py:46-57 re-derives the
+    required Eb/N0 from that grid)."""
+    if mode == "fixed-ber":
+        return [list(ax)] + [list(ber_grid[i, j]) for i in range(ber_grid.shape[0]) for j in range(ber_grid.shape[1])]
+    return [list(ax)] + [list(r) for r in rows]
 
 
 def axis(spec):
@@ -156,6 +181,7 @@ def main():
     eng = LinkEngine(local)
     eng.configure(constel_size=a.constel, n_ant=a.n_ant, pa=a.pa, ibo_db=axis(a.ibo)[0], channel=a.channel, receiver=a.receiver)
     t0 = time.time()
+    _ber = None
     if a.sweep == "nant-chan":
         ax, rows, frames = run_nant_chan(eng, a, rank, world, exchange)
     elif a.sweep == "fixed-ber":
@@ -164,12 +190,10 @@ def main():
         ax, rows, frames = run_sweep(eng, a, rank, world, exchange)
     dt = time.time() - t0
     if rank == 0:
-        data = [list(ax)] + [list(r) for r in rows]
         if a.out:
-            with open(a.out, "w", newline="") as fh:
-                csv.writer(fh).writerows(data)
+            write_csv(a.out, csv_rows(a.sweep, ax, rows, _ber if a.sweep == "fixed-ber" else None))
         print("--- Computation time: %f ---  (%d frames, %.0f frames/s, %d GPU)" % (dt, frames, frames / dt, world))
-        for r in data:
+        for r in [list(ax)] + [list(r) for r in rows]:   # fixed-ber: the required Eb/N0 per iteration (rows) and IBO (columns)
             print(" ".join("%.3e" % v for v in r))
     eng.close()
     if world > 1:
