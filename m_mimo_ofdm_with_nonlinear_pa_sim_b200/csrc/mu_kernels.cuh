@@ -57,11 +57,23 @@ __global__ void __launch_bounds__(256) k_prep_mu(const MuPrepArgs a) {
             // sub-carrier (antenna_array.py:240-257; the sqrt(K-U) factor cancels in the normalisation).
             // ||V||_F^2 = trace(inv(G)^H G inv(G)) = trace(inv(G)) = (g00 + g11) / det       (G is Hermitian)
             const double det = g00[jp] * g11[jp] - (g01r[jp] * g01r[jp] + g01i[jp] * g01i[jp]);
-            const double nrm = 1.0 / (det * sqrt((g00[jp] + g11[jp]) / det));
-            c00[jp] = g11[jp] * nrm;
-            c11[jp] = g00[jp] * nrm;
-            c01r[jp] = -g01r[jp] * nrm;   // inv(G)[0][1] = -g01 / det ; inv(G)[1][0] is its conjugate
-            c01i[jp] = -g01i[jp] * nrm;
+            const double tr = g00[jp] + g11[jp];
+            if (det > 1e-15 * tr * tr) {
+                const double nrm = 1.0 / (det * sqrt(tr / det));
+                c00[jp] = g11[jp] * nrm;
+                c11[jp] = g00[jp] * nrm;
+                c01r[jp] = -g01r[jp] * nrm;   // inv(G)[0][1] = -g01 / det ; inv(G)[1][0] is its conjugate
+                c01i[jp] = -g01i[jp] * nrm;
+            } else {
+                // Collinear users (e.g. co-located): G is singular, np.linalg.inv raises and the reference falls back to
+                // np.linalg.pinv (antenna_array.py:243-251; smallest / largest eigenvalue ~ det / tr^2 under pinv's 1e-15
+                // cut-off).  Rank one: G = tr u u^H, so pinv(G) = G / tr^2 and ||V||_F^2 = trace(pinv(G)) = 1 / tr.
+                const double nrm = 1.0 / (tr * sqrt(tr));
+                c00[jp] = g00[jp] * nrm;
+                c11[jp] = g11[jp] * nrm;
+                c01r[jp] = g01r[jp] * nrm;
+                c01i[jp] = g01i[jp] * nrm;
+            }
         }
     }
     // precoders out + per-antenna power summed over users (corrector.py:383)

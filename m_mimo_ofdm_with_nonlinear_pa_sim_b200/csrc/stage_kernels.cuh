@@ -377,12 +377,19 @@ __global__ void k_precoding(const PrecArgs a) {
             gr[p][q] = sr; gi[p][q] = si;
             ir[p][q] = (p == q) ? 1.0 : 0.0; ii[p][q] = 0.0;
         }
-    for (int c = 0; c < U; ++c) {  // Gauss-Jordan with partial pivoting
+    double gmax = 0.0;
+    for (int p = 0; p < U; ++p) gmax = fmax(gmax, gr[p][p]);
+    bool singular = false;
+    double g0r[MAX_USERS][MAX_USERS], g0i[MAX_USERS][MAX_USERS];  // the Gram matrix itself, for the pseudo-inverse path
+    for (int p = 0; p < U; ++p)
+        for (int q = 0; q < U; ++q) { g0r[p][q] = gr[p][q]; g0i[p][q] = gi[p][q]; }
+    for (int c = 0; c < U && !singular; ++c) {  // Gauss-Jordan with partial pivoting
         int piv = c; double best = gr[c][c] * gr[c][c] + gi[c][c] * gi[c][c];
         for (int r = c + 1; r < U; ++r) {
             const double m = gr[r][c] * gr[r][c] + gi[r][c] * gi[r][c];
             if (m > best) { best = m; piv = r; }
         }
+        if (best <= 1e-30 * gmax * gmax) { singular = true; break; }  // np.linalg.inv would raise here (or return garbage)
         if (piv != c)
             for (int q = 0; q < U; ++q) {
                 double t;
@@ -406,6 +413,55 @@ __global__ void k_precoding(const PrecArgs a) {
                 ir[r][q] -= fr * ir[c][q] - fi * ii[c][q]; ii[r][q] -= fr * ii[c][q] + fi * ir[c][q];
             }
         }
+    }
+    if (singular) {
+        // antenna_array.py:243-251: the reference retries with np.linalg.pinv.  Pseudo-inverse of the Hermitian Gram matrix
+        // by cyclic complex Jacobi rotations: G = W diag(w) W^H, pinv = W diag(1 / w_i for w_i > 1e-15 w_max) W^H.
+        double wr[MAX_USERS][MAX_USERS], wi[MAX_USERS][MAX_USERS];
+        for (int p = 0; p < U; ++p)
+            for (int q = 0; q < U; ++q) { wr[p][q] = (p == q) ? 1.0 : 0.0; wi[p][q] = 0.0; }
+        for (int sweep = 0; sweep < 24; ++sweep) {
+            double off = 0.0;
+            for (int p = 0; p < U; ++p)
+                for (int q = p + 1; q < U; ++q) off += g0r[p][q] * g0r[p][q] + g0i[p][q] * g0i[p][q];
+            if (off <= 1e-60 * gmax * gmax) break;
+            for (int p = 0; p < U; ++p)
+                for (int q = p + 1; q < U; ++q) {
+                    const double m = sqrt(g0r[p][q] * g0r[p][q] + g0i[p][q] * g0i[p][q]);
+                    if (m <= 1e-300) continue;
+                    const double er = g0r[p][q] / m, ei = g0i[p][q] / m;          // e^{i phi} of the pivot element
+                    const double tau = (g0r[q][q] - g0r[p][p]) / (2.0 * m);
+                    const double tt = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
+                    const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = tt * cs;
+                    // R = I except R[p][p] = c, R[p][q] = s e^{i phi}, R[q][p] = -s e^{-i phi}, R[q][q] = c;  G <- R^H G R
+                    for (int k2 = 0; k2 < U; ++k2) {  // columns p, q of G R
+                        const double apr = g0r[k2][p], api = g0i[k2][p], aqr = g0r[k2][q], aqi = g0i[k2][q];
+                        g0r[k2][p] = cs * apr - sn * (aqr * er + aqi * ei);  g0i[k2][p] = cs * api - sn * (aqi * er - aqr * ei);
+                        g0r[k2][q] = cs * aqr + sn * (apr * er - api * ei);  g0i[k2][q] = cs * aqi + sn * (api * er + apr * ei);
+                        const double vpr = wr[k2][p], vpi = wi[k2][p], vqr = wr[k2][q], vqi = wi[k2][q];
+                        wr[k2][p] = cs * vpr - sn * (vqr * er + vqi * ei);   wi[k2][p] = cs * vpi - sn * (vqi * er - vqr * ei);
+                        wr[k2][q] = cs * vqr + sn * (vpr * er - vpi * ei);   wi[k2][q] = cs * vqi + sn * (vpi * er + vpr * ei);
+                    }
+                    for (int k2 = 0; k2 < U; ++k2) {  // rows p, q of R^H (G R)
+                        const double apr = g0r[p][k2], api = g0i[p][k2], aqr = g0r[q][k2], aqi = g0i[q][k2];
+                        g0r[p][k2] = cs * apr - sn * (aqr * er - aqi * ei);  g0i[p][k2] = cs * api - sn * (aqi * er + aqr * ei);
+                        g0r[q][k2] = cs * aqr + sn * (apr * er + api * ei);  g0i[q][k2] = cs * aqi + sn * (api * er - apr * ei);
+                    }
+                }
+        }
+        double wmax = 0.0;
+        for (int p = 0; p < U; ++p) wmax = fmax(wmax, g0r[p][p]);
+        for (int p = 0; p < U; ++p)
+            for (int q = 0; q < U; ++q) {
+                double sr = 0.0, si = 0.0;
+                for (int e = 0; e < U; ++e) {
+                    if (!(g0r[e][e] > 1e-15 * wmax)) continue;
+                    const double iw = 1.0 / g0r[e][e];   // W[p][e] conj(W[q][e]) / w_e
+                    sr += (wr[p][e] * wr[q][e] + wi[p][e] * wi[q][e]) * iw;
+                    si += (wi[p][e] * wr[q][e] - wr[p][e] * wi[q][e]) * iw;
+                }
+                ir[p][q] = sr; ii[p][q] = si;
+            }
     }
     double fro = 0.0;
     for (int pass = 0; pass < 2; ++pass) {

@@ -157,7 +157,7 @@ class Link():
         if self.csi_epsylon is not None:
             self.my_csi_noise.rng_gen = np.random.default_rng(seed_arr[3])
         iters = np.asarray(cnc_n_iter_lst).astype(np.int64).reshape(-1)
-        if self._fused_ok():
+        if self._fused_ok(bool(reroll_chan)) and (iters.size == 0 or int(iters.max()) <= 62):  # the fused kernel runs up to 62 iterations
             self._simulate_fused(bool(incl_clean_run), bool(reroll_chan), iters, seed_arr, n_err_shared_arr, n_bits_sent_shared_arr)
         else:
             self._simulate_composed(bool(incl_clean_run), bool(reroll_chan), iters, n_err_shared_arr, n_bits_sent_shared_arr)
@@ -216,14 +216,17 @@ class Link():
                 bits_arr[slot] += self.n_bits_per_ofdm_sym
 
     # -- fused path: batches of frames through mmimo_link_simulate ------------------------------------------
-    def _fused_ok(self) -> bool:
+    def _fused_ok(self, reroll_chan: bool = True) -> bool:
         if os.environ.get("MMIMO_LINK_PATH", "fused") != "fused" or self.is_quadriga:
             return False
         m = self.my_mod
         if (m.n_fft, m.n_sub_carr, m.n_users) != (4096, 2048, 1) or m.constel_size not in (4, 16, 64, 256):
             return False
         if type(self.my_miso_chan) not in (channel.MisoLosFd, channel.MisoTwoPathFd, channel.MisoRayleighFd):
-            return False
+            # any other channel object (MisoRandomPathsFd, a user's own class) is carried by its channel_mat_fd: possible
+            # when the channel stays fixed; re-rolling needs calc_channel_mat / reroll_channel_coeffs of a known type
+            if reroll_chan or not hasattr(self.my_miso_chan, "channel_mat_fd"):
+                return False
         arr = self.my_array
         if arr.n_elements > 256 or arr._uniform() is None:
             return False
@@ -246,7 +249,8 @@ class Link():
             self._engine_pid = os.getpid()
         arr, rx, m = self.my_array, self.my_standard_rx, self.my_mod
         e0 = arr.array_elements[0]
-        kind = {channel.MisoLosFd: "los", channel.MisoTwoPathFd: "two_path", channel.MisoRayleighFd: "rayleigh"}[type(self.my_miso_chan)]
+        kind = {channel.MisoLosFd: "los", channel.MisoTwoPathFd: "two_path",
+                channel.MisoRayleighFd: "rayleigh"}.get(type(self.my_miso_chan), "injected")
         pa = "rapp" if isinstance(e0.impairment, distortion.Rapp) else "softlim"
         tx_pos = np.array([[t.cord_x, t.cord_y, t.cord_z] for t in arr.array_elements], dtype=np.float64)
         self._engine.configure(constel_size=m.constel_size, n_ant=arr.n_elements, pa=pa, ibo_db=float(self.ibo_val_db),
@@ -374,6 +378,22 @@ class Link():
                     log.append(dict(det=np.array(out["det"][f]), err=np.array(epf[f]), n_iter=n_iter))
                 used += 1
             self._rewind(gens, states, used, n)
+            last = (inj, used - 1) if used > 0 else None
+        if reroll_chan and not philox and 'last' in locals() and last is not None:
+            self._leave_state_of(*last)
+
+    def _leave_state_of(self, inj, f):
+        """The reference leaves the objects in the state of the LAST simulated realisation (receiver position, channel
+        matrix, precoder, AGC vectors, McncReceiver.agc_corr_vec); scripts that read them after simulate(), or call
+        simulate(reroll_chan=False) next, see the same.  LOS / two-path channels in "numpy" RNG mode: re-create that
+        realisation through the building blocks (one channel + precoding + AGC evaluation per simulate() call).  Rayleigh
+        and "philox" mode keep the pre-call state."""
+        if "rx_pos" not in inj or isinstance(self.my_miso_chan, channel.MisoRayleighFd) or self.csi_epsylon is not None:
+            return  # (re-deriving a CSI-error channel would draw from my_noise.rng_gen and shift the noise stream)
+        x, y, z = (float(v) for v in inj["rx_pos"][f])
+        self.my_standard_rx.set_position(cord_x=x, cord_y=y, cord_z=z)
+        self.my_miso_chan.calc_channel_mat(tx_transceivers=self.my_array.array_elements, rx_transceiver=self.my_standard_rx)
+        self.set_precoding_and_recalculate_agc()
 
     def _fixed_channel(self, n, prefix):
         m = self.my_mod

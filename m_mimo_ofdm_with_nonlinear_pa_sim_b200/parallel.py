@@ -50,8 +50,10 @@ def monte_carlo_point(run_batch, n_slots: int, bits_per_frame: int, n_err_min: i
     between steps: every result slot counts frames until it holds `n_err_min` errors or `bits_sent_max` bits.
 
     run_batch(first_global_frame, n_frames, n_slots_active_mask) -> per-slot bit errors (length n_slots) of that
-    block of global frames on this rank's GPU.  A step covers `frames_per_step * world` global frames, clipped to
-    what the bit budget of the least advanced active slot still allows.
+    block of global frames on this rank's GPU.  A step covers `frames_per_step` GLOBAL frames (split over the ranks by
+    shard_range), clipped to what the bit budget of the least advanced active slot still allows - the stop rule is
+    applied between steps, so the step size is global on purpose: the set of simulated frames, and with it every counter,
+    is the same for any number of ranks.
     Returns (errors[n_slots], bits[n_slots], frames_simulated_globally)."""
     exchange = exchange or CounterExchange(world)
     err = np.zeros(n_slots, dtype=np.int64)
@@ -62,7 +64,7 @@ def monte_carlo_point(run_batch, n_slots: int, bits_per_frame: int, n_err_min: i
         if not active.any():
             break
         left = int(np.ceil((bits_sent_max - int(bits[active].min())) / bits_per_frame))
-        n_glob = max(1, min(frames_per_step * world, left))
+        n_glob = max(1, min(frames_per_step, left))
         start, count = shard_range(n_glob, rank, world)
         e = np.zeros(n_slots, dtype=np.int64)
         if count > 0:

@@ -37,3 +37,8 @@ def pytest_sessionfinish(session, exitstatus):
         parity_util.dump_stats()
     except Exception:
         pass
+    try:
+        import ci_util
+        ci_util.dump_log()   # z statistics of the BER-vs-reference comparisons -> $MMIMO_CI_LOG
+    except Exception:
+        pass

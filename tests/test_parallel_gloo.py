@@ -70,8 +70,8 @@ def test_two_ranks_gloo_match_one_rank():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    ref_a = monte_carlo_point(fake_errors, N_SLOTS, BITS, 10 ** 12, BITS * 101, 32)   # same global step: 16 x 2
-    ref_b = monte_carlo_point(fake_errors, N_SLOTS, BITS, 20000, BITS * 10000, 8)     # same global step: 4 x 2
+    ref_a = monte_carlo_point(fake_errors, N_SLOTS, BITS, 10 ** 12, BITS * 101, 16)   # the SAME arguments on one rank
+    ref_b = monte_carlo_point(fake_errors, N_SLOTS, BITS, 20000, BITS * 10000, 4)
     for rank, a, b in res:
         assert a[0] == ref_a[0].tolist() and a[1] == ref_a[1].tolist() and a[2] == ref_a[2]
         assert b[0] == ref_b[0].tolist() and b[1] == ref_b[1].tolist() and b[2] == ref_b[2]
