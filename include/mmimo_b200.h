@@ -240,6 +240,12 @@ enum { MMIMO_PREC_PHASE = 0, MMIMO_PREC_MRT = 1, MMIMO_PREC_ZF = 2 };
  * `rows` orthonormal transforms of length n; `skip` leading samples of every input row are dropped (cyclic prefix
  * removal), `cp` trailing output samples are repeated in front of every output row (cyclic prefix insertion). */
 int mmimo_fft(mmimo_ctx* ctx, int inverse, int n, int rows, int skip, int cp, const float* in, float* out);
+/* scipy.signal.welch as the reference's scripts call it - welch(x, fs=fs, nfft=nfft, nperseg=nperseg, return_onesided=False)
+ * with scipy's defaults (periodic Hann window, 50 % overlap, constant detrend, density scaling, mean over segments):
+ * main_multiuser/main_multiuser_mrt_precoding_radiation_pattern.py:371-381 (and the PSD blocks of the other beampattern / PSD
+ * scripts).  x: n complex samples; psd [nfft] doubles in FFT-bin order, freqs [nfft] = fftfreq(nfft, 1 / fs) (may be NULL).
+ * nfft a power of two in 8..8192, nperseg <= nfft. */
+int mmimo_welch_psd(mmimo_ctx* ctx, size_t n, const float* x, int nperseg, int nfft, double fs, double* freqs, double* psd);
 /* SoftLimiter/Rapp/ThirdOrderNonLin.process (distortion.py:91-98, :191-198, :281) on n complex samples */
 int mmimo_pa_process(mmimo_ctx* ctx, const mmimo_pa_desc* pa, size_t n, const float* in, float* out);
 /* modulation.modulate (modulation.py:13-25): bits -> n_sym constellation points */

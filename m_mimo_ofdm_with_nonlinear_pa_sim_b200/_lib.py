@@ -61,7 +61,7 @@ EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_er
            "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_sweep", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
            "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
-           "mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
+           "mmimo_fft", "mmimo_welch_psd", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
            "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
            "mmimo_channel_geometric", "mmimo_channel_fspl", "mmimo_channel_random_paths", "mmimo_precoding",
            "mmimo_agc", "mmimo_cnc_receive", "mmimo_mcnc_receive"]

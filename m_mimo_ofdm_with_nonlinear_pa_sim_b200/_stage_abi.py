@@ -26,7 +26,7 @@ class PaDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("p0", C.c_double), ("p1", C.c_double)]
 
 
-STAGE_EXPORTS = ["mmimo_fft", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
+STAGE_EXPORTS = ["mmimo_fft", "mmimo_welch_psd", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
                  "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
                  "mmimo_channel_geometric", "mmimo_channel_fspl", "mmimo_channel_random_paths", "mmimo_precoding",
                  "mmimo_agc", "mmimo_cnc_receive", "mmimo_mcnc_receive"]
@@ -36,6 +36,7 @@ def bind(lib):
     vp, i, sz, d = C.c_void_p, C.c_int, C.c_size_t, C.c_double
     md, pd = C.POINTER(ModemDesc), C.POINTER(PaDesc)
     lib.mmimo_fft.argtypes = [vp, i, i, i, i, i, c_f_p, c_f_p]
+    lib.mmimo_welch_psd.argtypes = [vp, sz, c_f_p, i, i, d, c_d_p, c_d_p]
     lib.mmimo_pa_process.argtypes = [vp, pd, sz, c_f_p, c_f_p]
     lib.mmimo_qam_map.argtypes = [vp, md, sz, c_u8_p, c_f_p]
     lib.mmimo_qam_detect.argtypes = [vp, md, sz, c_f_p, c_f_p, c_u8_p]
@@ -121,6 +122,15 @@ class StageOps:
         bits = np.empty(s.size * bps, dtype=np.uint8) if want_bits else None
         self._call(self._lib.mmimo_qam_detect, C.byref(md), s.size, _p(s, C.c_float), _p(sym, C.c_float), _p(bits, C.c_uint8))
         return (sym.astype(np.complex128) if want_symbols else None, bits.view(np.int8) if want_bits else None)
+
+    def welch_psd(self, x, fs, nfft, nperseg):
+        """scipy.signal.welch(x, fs=fs, nfft=nfft, nperseg=nperseg, return_onesided=False) -> (freqs, psd), float64"""
+        x = _c64(x).reshape(-1)
+        freqs = np.empty(int(nfft), dtype=np.float64)
+        psd = np.empty(int(nfft), dtype=np.float64)
+        self._call(self._lib.mmimo_welch_psd, x.size, _p(x, C.c_float), int(nperseg), int(nfft), float(fs), _p(freqs, C.c_double),
+                   _p(psd, C.c_double))
+        return freqs, psd
 
     def qam_soft_llr(self, md, symbols, noise_var):
         """modulation.soft_decoding (modulation.py:29-59): float64 LLRs, MSB of each symbol first"""

@@ -23,7 +23,7 @@ namespace mmimo {
 #define T64_DEPTH 4  // level-C table entries fetched this many butterfly classes ahead of their use
 #endif
 #ifndef T64_ACC_SMEM
-#define T64_ACC_SMEM 14  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
+#define T64_ACC_SMEM 11  // of the 32 per-thread accumulators, how many live in (thread-private) shared memory
 #endif
 #ifndef T64_PRUNE
 #define T64_PRUNE 1  // guard-band pruning of the first transform's level A and of the second transform's last level
@@ -32,7 +32,11 @@ namespace mmimo {
 #define T64_LOOP 1  // 1: guard-band form of level A of the first transform ahead of the loop; 2: loop starts with level A
 #endif
 #ifndef T64_SYNC
-#define T64_SYNC 0  // group-barrier placement, see the kernel (0 measured faster with 14 shared accumulators, 1 with 12)
+#define T64_SYNC 1  // group-barrier placement, see the kernel
+#endif
+#ifndef T64_RING
+#define T64_RING 2  // the groups take turns in the shared-memory exchange (token ring over named barriers): 1 stores + loads,
+                   // 2 stores only (measured best), 3 one token for the stores and one for the loads; 0 off
 #endif
 #ifndef T64_PA_UNIT
 #define T64_PA_UNIT 1  // PA evaluated on the signal scaled to a unit threshold (one multiply less per sample)
@@ -90,6 +94,15 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     unsigned phA = 0, phB = 0;  // parities of the mbarrier phases to wait for next
+#ifndef T64_RING_ORDER
+#define T64_RING_ORDER 0  // token order 0: 0,1,2,3 (measured best with the store-only token) ; 1: 0,2,1,3 ; 2: 0,1,3,2
+#endif
+    // successor of group g in the ring (one nibble per group)
+    const int ring_next = ((T64_RING_ORDER == 1 ? 0x0132 : T64_RING_ORDER == 2 ? 0x2031 : 0x0321) >> (4 * g)) & 3;
+    if (T64_RING && ring_next == 0) {  // the token(s) start with group 0
+        asm volatile("bar.arrive %0, 128;" ::"r"(5) : "memory");
+        if (T64_RING == 3) asm volatile("bar.arrive %0, 128;" ::"r"(9) : "memory");
+    }
     const t64::TabA tab_a = t64::load_tab_a(tab, lane);
     // mirrored source slot of register i: (64 - lane) + 64 (31 - i); lane 0 keeps its column, where slot 0 holds
     // bin 1024: register 16 (i = 0, moved below) <- bin 3072 = slot 1024, register 48 (i = 16) <- bin 1024 = slot 0
@@ -182,6 +195,15 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                 acc[i] = pk(0.f, 0.f);
                 if (i < T64_ACC_SMEM) accx_s[i * FFT_THREADS] = pk(0.f, 0.f);
             }
+            // T64_RING: the exchange phases (64 STS.64 + 64 LDS.64 per thread, no FMA work) of the four groups are serialised
+            // in the fixed order g = 0, 1, 2, 3, 0, ... by a token that travels over named barriers 5 + g (128 = the 64
+            // waiting threads of group g + the 64 arriving threads of group g - 1).  Started together, all eight warps
+            // would hit the shared-memory pipe at once and leave the FMA pipe idle for that long; in the ring, one group
+            // exchanges while the others compute.  Every group passes the token exactly 2 * ceil(K / 4) times per pass.
+            auto ring_acquire = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(5 + g) : "memory"); };
+            auto ring_acquire2 = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(9 + g) : "memory"); };
+            auto ring_release2 = [&]() { asm volatile("bar.arrive %0, 128;" ::"r"(9 + ring_next) : "memory"); };
+            auto ring_release = [&]() { asm volatile("bar.arrive %0, 128;" ::"r"(5 + ring_next) : "memory"); };
             for (int k = g; k < K; k += R64_GROUPS) {
                 pf2 x[64];
                 mbar_wait_parity(mbB, phB);
@@ -251,9 +273,14 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     if (T64_LOOP != 1) t64::p1_level_a(x);
                     t64::p1_levels_bc(x);
                     if (T64_SYNC) sy.x_sync();  // S1
+                    if (T64_RING) ring_acquire();
                     t64::exchange_store(x, buf, lane);
                     sy.x_sync();                // S2
+                    if (T64_RING >= 2) ring_release();   // token covers the stores only
+                    if (T64_RING == 3) ring_acquire2();  // a second token for the loads
                     t64::pass2_load(x, buf, lane);
+                    if (T64_RING == 1) ring_release();
+                    if (T64_RING == 3) ring_release2();
                     t64::Raw3 rb[4];
                     if (!T64_SYNC) {
                         sy.x_sync();            // S3 (both transforms)
@@ -292,6 +319,13 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     }
 #pragma unroll
                     for (int i = 0; i < T64_ACC_SMEM; ++i) accx_s[i * FFT_THREADS] = av[i];
+                }
+            }
+            if (T64_RING) {  // groups with one chain less than the others still pass the token on
+                const int mine = K > g ? (K - g + R64_GROUPS - 1) / R64_GROUPS : 0, slots = (K + R64_GROUPS - 1) / R64_GROUPS;
+                for (int e = 2 * mine; e < 2 * slots; ++e) {
+                    ring_acquire(); ring_release();
+                    if (T64_RING == 3) { ring_acquire2(); ring_release2(); }
                 }
             }
             // ---- the four groups' partial sums meet in the (idle) exchange buffers: fixed summation order ----

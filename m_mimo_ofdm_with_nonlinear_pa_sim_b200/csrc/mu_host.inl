@@ -142,7 +142,12 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             pa.ibo_lin = mp.ibo_lin; pa.avg_symbol_power = mp.avg_symbol_power; pa.avg_sample_power = mp.avg_sample_power;
             pa.snr_lin = mp.snr_lin;
             k_prep_realisation<false><<<ni, 256, 0, c->stream>>>(pa, SweepArgs{});
-            k_copy_loop_p0<<<nblk(ni), 256, 0, c->stream>>>(c->scal.as<FrameScalars>(), c->s_d.as<FrameScalars>(), ni);
+            // With zero forcing the script's single-user arrays (n_users = 1) get their PA saturation power from the phase-only
+            // precoder of antenna_array.py:175-178 (mean |v|^2 = 1: ibo * avg_sample_power) before McncReceiver.__init__
+            // overwrites the precoder with MRT (corrector.py:135) - reproduced as written (tests/golden/mu_su_loop.npz)
+            const bool phase_pa = rq->precoding == MMIMO_MU_ZF && (cfg.pa_kind == MMIMO_PA_SOFT_LIMITER || cfg.pa_kind == MMIMO_PA_RAPP);
+            k_copy_loop_p0<<<nblk(ni), 256, 0, c->stream>>>(c->scal.as<FrameScalars>(), c->s_d.as<FrameScalars>(), ni,
+                                                          phase_pa ? (float)(mp.ibo_lin * mp.avg_sample_power) : 0.f);
             c->launches += 2;
             fa.loop.v = nullptr; fa.loop.v_fs = 0;
             fa.loop.sscale = c->s_a.as<float>(); fa.loop.sscale_fs = N_SC;

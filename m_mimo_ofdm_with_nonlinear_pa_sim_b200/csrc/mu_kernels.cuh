@@ -157,10 +157,10 @@ __global__ void __launch_bounds__(256) k_prep_mu(const MuPrepArgs a) {
     }
 }
 
-// loop-side PA parameter of the single-user receivers: scal_mu[i].pa_p0_loop = scal_su[i].pa_p0_tx
-__global__ void k_copy_loop_p0(FrameScalars* mu, const FrameScalars* su, int n) {
+// loop-side PA parameter of the single-user receivers: scal_mu[i].pa_p0_loop = scal_su[i].pa_p0_tx, or `fixed` (> 0) for all
+__global__ void k_copy_loop_p0(FrameScalars* mu, const FrameScalars* su, int n, float fixed) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) mu[i].pa_p0_loop = su[i].pa_p0_tx;
+    if (i < n) mu[i].pa_p0_loop = fixed > 0.f ? fixed : su[i].pa_p0_tx;
 }
 
 }  // namespace mmimo

@@ -125,6 +125,45 @@ extern "C" int mmimo_fft(mmimo_ctx* c, int inverse, int n, int rows, int skip, i
     return 0;
 }
 
+extern "C" int mmimo_welch_psd(mmimo_ctx* c, size_t n, const float* x, int nperseg, int nfft, double fs, double* freqs, double* psd) {
+    STAGE_PROLOGUE(c);
+    if (!x || !psd) return fail("mmimo_welch_psd: NULL buffer");
+    if (nfft < 8 || nfft > 8192 || (nfft & (nfft - 1))) return fail("mmimo_welch_psd: nfft must be a power of two in 8..8192 (got %d)", nfft);
+    if (nperseg < 2 || nperseg > nfft) return fail("mmimo_welch_psd: nperseg must be 2..nfft (got %d)", nperseg);
+    if ((size_t)nperseg > n) return fail("mmimo_welch_psd: the signal is shorter than one segment (%zu < %d)", n, nperseg);
+    if (!(fs > 0.0)) return fail("mmimo_welch_psd: fs must be positive");
+    const int step = nperseg - nperseg / 2;                       // noverlap = nperseg // 2 (scipy default)
+    const size_t n_seg = (n - (size_t)(nperseg / 2)) / (size_t)step;
+    const size_t seg_chunk = std::min<size_t>(n_seg, std::max<size_t>(1, ((size_t)256 << 20) / ((size_t)nfft * 16)));
+    if (ar.begin(Arena::pad(n * 8) + 2 * Arena::pad(seg_chunk * nfft * 8) + Arena::pad((size_t)nfft * 8))) return 1;
+    float2* dx = ar.get<float2>(n);
+    float2* rows = ar.get<float2>(seg_chunk * nfft);
+    float2* spec = ar.get<float2>(seg_chunk * nfft);
+    double* acc = ar.get<double>(nfft);
+    CK(cudaMemcpyAsync(dx, x, n * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemsetAsync(acc, 0, (size_t)nfft * 8, c->stream));
+    for (size_t s0 = 0; s0 < n_seg; s0 += seg_chunk) {
+        const int ns = (int)std::min(seg_chunk, n_seg - s0);
+        k_welch_segments<<<ns, 256, 0, c->stream>>>(dx + s0 * step, rows, nperseg, step, nfft);
+        c->launches++;
+        if (fft_dev(c, false, nfft, ns, 0, 0, rows, spec)) return 1;
+        k_welch_reduce<<<(nfft + 255) / 256, 256, 0, c->stream>>>(spec, acc, ns, nfft);
+        c->launches++;
+    }
+    // density scaling 1 / (fs sum w^2), mean over segments, and nfft to undo the orthonormal transform; for the periodic Hann
+    // window sum_n w_n^2 = 3 N / 8 (N >= 3)
+    double w2 = 0.0;
+    for (int i = 0; i < nperseg; ++i) { const double w = 0.5 - 0.5 * cos(2.0 * M_PI * i / nperseg); w2 += w * w; }
+    k_scale_d<<<(nfft + 255) / 256, 256, 0, c->stream>>>(acc, (double)nfft / (fs * w2 * (double)n_seg), nfft);
+    c->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(psd, acc, (size_t)nfft * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (freqs)  // np.fft.fftfreq(nfft, 1 / fs)
+        for (int i = 0; i < nfft; ++i) freqs[i] = (double)(i < (nfft + 1) / 2 ? i : i - nfft) * fs / nfft;
+    return 0;
+}
+
 extern "C" int mmimo_pa_process(mmimo_ctx* c, const mmimo_pa_desc* pa, size_t n, const float* in, float* out) {
     STAGE_PROLOGUE(c);
     if (!pa || !in || !out) return fail("mmimo_pa_process: NULL argument");

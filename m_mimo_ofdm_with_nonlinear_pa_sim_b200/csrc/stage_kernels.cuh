@@ -584,6 +584,55 @@ __global__ void k_rx_estimate(const float2* __restrict__ x, const float2* __rest
     dist_est[s] = make_float2(acc.x - sy.x * scale, acc.y - sy.y * scale);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Welch power spectral density as the reference's scripts call scipy.signal.welch
+// (main_multiuser/main_multiuser_mrt_precoding_radiation_pattern.py:371-381 and 59 more call sites):
+//   welch(x, fs, nfft, nperseg, return_onesided=False) with scipy's defaults window="hann" (periodic), noverlap =
+//   nperseg // 2, detrend="constant", scaling="density", average="mean".
+// k_welch_segments: one CTA per segment: mean removal (double), window, zero padding to nfft -> rows [n_seg][nfft];
+// the rows go through the batched stage FFT; k_welch_reduce averages |X|^2 over the segments per bin (double).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_welch_segments(const float2* __restrict__ x, float2* __restrict__ rows, int nperseg,
+                                                        int step, int nfft) {
+    __shared__ double red_s[16];
+    const int seg = blockIdx.x, t = threadIdx.x;
+    const float2* __restrict__ xs = x + (size_t)seg * step;
+    double sr = 0.0, si = 0.0;
+    for (int i = t; i < nperseg; i += 256) { sr += xs[i].x; si += xs[i].y; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { sr += __shfl_xor_sync(0xffffffffu, sr, o); si += __shfl_xor_sync(0xffffffffu, si, o); }
+    if ((t & 31) == 0) { red_s[t >> 5] = sr; red_s[8 + (t >> 5)] = si; }
+    __syncthreads();
+    double mr = 0.0, mi = 0.0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { mr += red_s[w]; mi += red_s[8 + w]; }
+    mr /= nperseg; mi /= nperseg;
+    float2* __restrict__ out = rows + (size_t)seg * nfft;
+    for (int i = t; i < nfft; i += 256) {
+        float2 v = make_float2(0.f, 0.f);
+        if (i < nperseg) {
+            const double w = 0.5 - 0.5 * cospi(2.0 * (double)i / (double)nperseg);  // scipy get_window("hann", N): periodic
+            v = make_float2((float)(((double)xs[i].x - mr) * w), (float)(((double)xs[i].y - mi) * w));
+        }
+        out[i] = v;
+    }
+}
+// acc[f] += sum_seg |X[seg][f]|^2 (the stage FFT is orthonormal; the caller's scale restores the plain DFT)
+__global__ void __launch_bounds__(256) k_welch_reduce(const float2* __restrict__ rows, double* __restrict__ acc, int n_seg, int nfft) {
+    const int f = blockIdx.x * 256 + threadIdx.x;
+    if (f >= nfft) return;
+    double s = 0.0;
+    for (int g = 0; g < n_seg; ++g) {
+        const float2 v = rows[(size_t)g * nfft + f];
+        s += (double)v.x * v.x + (double)v.y * v.y;
+    }
+    acc[f] += s;
+}
+__global__ void k_scale_d(double* __restrict__ x, double s, int n) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < n) x[i] *= s;
+}
+
 }  // namespace mmimo
 
 static int stage_kernels_init();

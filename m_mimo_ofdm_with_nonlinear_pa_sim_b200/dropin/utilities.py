@@ -101,6 +101,19 @@ def to_time_domain(in_sig_mat_fd: ndarray) -> ndarray:
 
 
 # ---- result files / console (utilities.py:342-392) -----------------------------------------------
+def welch(x, fs: float = 1.0, nfft: int = None, nperseg: int = None, return_onesided: bool = False):
+    """Power spectral density on the device with the call signature the reference's PSD blocks use for scipy.signal.welch
+    (main_multiuser/main_multiuser_mrt_precoding_radiation_pattern.py:371-381): complex input, two-sided, periodic Hann window,
+    50 % overlap, constant detrend, density scaling.  `from utilities import welch` in place of `from scipy.signal import
+    welch` moves the PSD blocks of the beampattern scripts to the GPU.  Returns (freqs, psd) like scipy."""
+    if return_onesided:
+        raise ValueError("the device PSD is two-sided (the reference always passes return_onesided=False for its complex signals)")
+    x = np.asarray(x).ravel()
+    nperseg = int(nperseg) if nperseg is not None else min(256, x.size)
+    nfft = int(nfft) if nfft is not None else nperseg
+    return get_ops().welch_psd(x, float(fs), nfft, nperseg)
+
+
 def save_to_csv(data_lst: list, filename: str) -> None:
     with open("figs/csv_results/%s.csv" % filename, 'w', newline='') as csv_file:
         csv.writer(csv_file).writerows(data_lst)

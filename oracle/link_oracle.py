@@ -613,7 +613,14 @@ def mu_frame(cfg: LinkConfig, h_list, tx_idx, noise_fd, n_iter_max, precoding="m
             d = cnc_receive(cfg, y, cnc_pa_params(cfg), alpha, n_iter_max, other_usr_symbols=other, trace=tr)
         elif receiver == "mcnc_su":
             su = make_realisation(cfg, h_list[u])
-            d = mcnc_receive(cfg, y, su.h_loop, su.v, su.pa, su.ak_hk_vk_agc, n_iter_max, trace=tr)
+            pa_su = su.pa
+            if precoding == "zf" and cfg.pa_kind in (PA_SOFT_LIMITER, PA_RAPP):
+                # script :563-571 with zf_precoding: the single-user copy of the array (n_users = 1) takes the phase-only
+                # branch of set_precoding_matrix (antenna_array.py:175-178), update_distortion fixes the PA saturation power
+                # from THAT precoder (mean |v|^2 = 1), and McncReceiver.__init__ then overwrites the precoder with MRT
+                # (corrector.py:135) without touching the PA: MRT loop, saturation power ibo * avg_sample_power * 1
+                pa_su = (su.pa[0], np.power(10, cfg.ibo_db / 10) * cfg.avg_sample_power, su.pa[2])
+            d = mcnc_receive(cfg, y, su.h_loop, su.v, pa_su, su.ak_hk_vk_agc, n_iter_max, trace=tr)
         else:
             d = mcnc_receive(cfg, y, h_list[u], real["v"], real["pa"], real["agc"][u], n_iter_max,
                              other_usr_idx=tx_idx[1 - u], usr_idx=u, trace=tr)
@@ -663,7 +670,7 @@ def draw_channel(cfg: LinkConfig, rx_pos, rayleigh_state=None):
 
 def link_simulate(cfg: LinkConfig, snr_db: float, n_iter_max: int, seeds, n_frames: int, is_mcnc=True,
                   incl_clean_run=False, reroll_chan=True, csi_eps=None, rayleigh_seed=1234,
-                  return_frames=False):
+                  return_frames=False, h_fixed=None):
     """Fixed-frame-count version of Link.simulate (mp_model.py:89-222) for ONE worker, consuming the
     same numpy PCG64 streams in the same order: seeds = (bits, noise, location[, csi]).
     All iterations 0..n_iter_max are recorded for every frame (the reference stops recording an
@@ -681,7 +688,11 @@ def link_simulate(cfg: LinkConfig, snr_db: float, n_iter_max: int, seeds, n_fram
         rayleigh_coeffs(r, cfg.n_ant, cfg.n_fft)  # the constructor's own draw, channel.py:229
         ray_state = (r, att)
     rx_pos = cfg.rx_pos
-    h = draw_channel(cfg, rx_pos, ray_state) if (cfg.channel != "rayleigh" or not reroll_chan) else None
+    if h_fixed is not None:  # any channel object with reroll_chan=False: the matrix it holds (mp_model.py:190-200)
+        assert not reroll_chan
+        h = np.asarray(h_fixed)
+    else:
+        h = draw_channel(cfg, rx_pos, ray_state) if (cfg.channel != "rayleigh" or not reroll_chan) else None
 
     def next_realisation():
         nonlocal h, rx_pos

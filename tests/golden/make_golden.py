@@ -62,11 +62,14 @@ def make_channel(kind, my_array, my_rx):
         ch.calc_channel_mat(tx_transceivers=my_array.array_elements, rx_transceiver=my_rx, skip_attenuation=False)
     elif kind == "rayleigh":
         ch = channel.MisoRayleighFd(tx_transceivers=my_array.array_elements, rx_transceiver=my_rx, seed=1234)
+    elif kind == "random_paths":
+        ch = channel.MisoRandomPathsFd(tx_transceivers=my_array.array_elements, rx_transceiver=my_rx, seed=5, n_paths=8,
+                                       max_delay_spread=1e-6)
     return ch
 
 
 def golden_link(name, n_ant, chan_kind, ibo, ebn0, n_frames, iters, seeds, is_mcnc=True, incl_clean=False,
-                csi_eps=None, n_fft=4096, n_sc=2048, constel=64, pa="softlim", full_frames=None):
+                csi_eps=None, n_fft=4096, n_sc=2048, constel=64, pa="softlim", full_frames=None, reroll=True):
     """mp_model.Link.simulate driven exactly like main_mp_miso_mcnc_ber_vs_ebn0.py:101-134 (one worker).
     full_frames: many-frame cases keep the bulky float64 arrays (noise, channel row, AGC) for the first `full_frames`
     frames only and the equalised signal as complex64; decisions, error counters, positions and PA powers of ALL
@@ -118,7 +121,7 @@ def golden_link(name, n_ant, chan_kind, ibo, ebn0, n_frames, iters, seeds, is_mc
     n_res = len(iters) + (1 if incl_clean else 0)
     e = mp.Array(ctypes.c_double, n_res, lock=True)
     b = mp.Array(ctypes.c_double, n_res, lock=True)
-    link.simulate(incl_clean, True, iters, list(seeds), e, b)
+    link.simulate(incl_clean, reroll, iters, list(seeds), e, b)
 
     n_clean = n_frames if incl_clean else 0
     bins = np.concatenate((np.arange(n_fft - n_sc // 2, n_fft), np.arange(1, n_sc // 2 + 1)))
@@ -128,7 +131,7 @@ def golden_link(name, n_ant, chan_kind, ibo, ebn0, n_frames, iters, seeds, is_mc
     out = dict(
         n_ant=n_ant, chan=chan_kind, ibo_db=float(ibo), snr_db=snr_db, ebn0_db=float(ebn0), n_frames=n_frames,
         iters=iters, seeds=np.asarray(seeds, dtype=np.int64), is_mcnc=int(is_mcnc), incl_clean=int(incl_clean),
-        csi_eps=-1.0 if csi_eps is None else float(csi_eps), n_fft=n_fft, n_sc=n_sc, constel=constel, pa=pa,
+        csi_eps=-1.0 if csi_eps is None else float(csi_eps), n_fft=n_fft, n_sc=n_sc, constel=constel, pa=pa, reroll=int(reroll),
         err=np.array(list(e)), bits=np.array(list(b)),
         tx_idx=tx_idx,
         noise_sc=np.stack(rec["noise"])[:, bins],
@@ -343,6 +346,13 @@ if __name__ == "__main__":
     golden_link("link_k8_los_rapp", 8, "los", 1.0, 15.0, 2, [0, 1, 2], [41, 42, 43], pa="rapp")
     golden_link("link_k16_los_small", 16, "los", 0.0, 15.0, 4, [0, 1, 2, 3, 4, 5, 6, 7, 8], [51, 52, 53],
                 n_fft=1024, n_sc=512, constel=16)
+    golden_random_paths_fixed()
+
+
+def golden_random_paths_fixed():
+    """Link.simulate(reroll_chan=False) over a MisoRandomPathsFd channel (BASELINE config 3; the reference cannot re-roll this
+    channel through Link - it has no calc_channel_mat - but a fixed one works, mp_model.py:190-200)"""
+    golden_link("link_k8_random_paths_fixed", 8, "random_paths", 1.0, 16.0, 3, [0, 1, 2, 3], [61, 62, 63], reroll=False)
 
 
 def golden_full_size_extras():

@@ -168,3 +168,36 @@ def test_multiprocessing_runner_pattern(M, rng_mode):
     ber = err / bits
     assert ber[0] < 5e-3                                  # no distortion
     assert 0.05 < ber[1] < 0.14 and np.all(np.diff(ber[1:]) < 0)  # standard RX, then improving with MCNC iterations
+
+
+def test_fixed_random_paths_channel_through_the_fused_link(M):
+    """A channel object the fused path has no generator for (MisoRandomPathsFd, BASELINE config 3) with reroll_chan=False: the
+    drop-in Link injects the object's channel_mat_fd into the fused kernels; decisions and counters against the reference's
+    run of the same worker (tests/golden/link_k8_random_paths_fixed.npz) under the margin rule."""
+    from test_oracle_golden import random_paths_channel
+    g = load_golden("link_k8_random_paths_fixed")
+    mod, dist, tx, rx, arr = build_objects(M, 8, pa="softlim", ibo=0.0)
+    ch = M["channel"].MisoRandomPathsFd(tx_transceivers=arr.array_elements, rx_transceiver=rx, seed=5, n_paths=8,
+                                        max_delay_spread=1e-6)
+    link = M["mp_model"].Link(mod_obj=mod, array_obj=arr, std_rx_obj=rx, chan_obj=ch, noise_obj=M["noise"].Awgn(snr_db=10, seed=1234),
+                              rx_loc_var=10.0, n_err_min=int(1e12), bits_sent_max=12288 * int(g["n_frames"]), is_mcnc=True)
+    link.frame_log = []
+    link.update_distortion(ibo_val_db=float(g["ibo_db"]))
+    link.set_snr(snr_db_val=float(g["snr_db"]))
+    assert link._fused_ok(reroll_chan=False) and not link._fused_ok(reroll_chan=True)
+    iters = np.asarray(g["iters"])
+    e = mp.Array(ctypes.c_double, len(iters), lock=True)
+    b = mp.Array(ctypes.c_double, len(iters), lock=True)
+    link.simulate(False, False, iters, [int(s) for s in g["seeds"]], e, b)
+    assert np.array_equal(np.array(list(b)), g["bits"])
+    cfg = lo.LinkConfig(n_ant=8, ibo_db=float(g["ibo_db"]))
+    errs, bits, frames = lo.link_simulate(cfg, float(g["snr_db"]), int(iters.max()), list(g["seeds"]), int(g["n_frames"]),
+                                          reroll_chan=False, h_fixed=random_paths_channel(cfg), return_frames=True)
+    n_div = 0
+    for fr, rec in zip(frames, link.frame_log):
+        its = np.arange(rec["n_iter"] + 1)
+        n_ok = check_frame("drop-in Link fixed random-paths channel", rec["det"][its], fr["det"][its], np.stack(fr["corr"])[its], 64,
+                           rec["err"][its], fr["err"][its])
+        n_div += n_ok < len(its)
+    if n_div == 0:
+        assert np.array_equal(np.array(list(e)), g["err"])

@@ -234,3 +234,32 @@ def test_fused_norm_pass_is_bit_identical(engine):
         err += part["err"]
         assert np.array_equal(part["rx_eq"], big["rx_eq"][c0:c0 + 80])
     assert np.array_equal(err, big["err"])
+
+
+def test_closed_form_los_realisation_matches_oracle(monkeypatch):
+    """k_prep_los (closed form in the K path amplitudes, no pass over the channel rows) and k_prep_realisation
+    (MMIMO_PREP_ANALYTIC=0) against the oracle's realisation bookkeeping (antenna_array.py:163-171,313-360, mp_model.py:290-329)
+    for device-generated LOS channels at injected receiver positions; and both kernels give the same frames."""
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    cfg = lo.LinkConfig(n_ant=64, channel="los", ibo_db=1.5)
+    rng = np.random.default_rng(12)
+    pos = np.stack([lo.draw_rx_position(cfg, rng) for _ in range(4)])
+    snr = float(lo.ebn0_to_snr(15.0, cfg.n_sub_carr, cfg.n_sub_carr, 64))
+    outs = {}
+    for knob in ("1", "0"):
+        monkeypatch.setenv("MMIMO_PREP_ANALYTIC", knob)
+        eng = LinkEngine(0)
+        try:
+            eng.configure(n_ant=64, channel="los", ibo_db=1.5)
+            out = eng.simulate(4, 2, snr, seed=5, inject=dict(rx_pos=pos), dumps=("agc", "pa_p0", "alpha", "rx_eq", "det"))
+        finally:
+            eng.close()
+        outs[knob] = out
+        for i in range(4):
+            real = lo.make_realisation(cfg, lo.draw_channel(cfg, pos[i]))
+            assert rel_l2(out["agc"][i], real.ak_hk_vk_agc) < TOL, knob
+            assert abs(out["pa_p0"][i] / real.pa[1] - 1) < TOL, knob
+            assert np.allclose(out["alpha"][i], real.alpha_k, rtol=1e-5), knob
+    a, b = outs["1"], outs["0"]
+    assert rel_l2(a["rx_eq"], b["rx_eq"]) < 2e-6
+    assert (a["det"] != b["det"]).mean() < 1e-3 and np.abs(a["err"].astype(np.int64) - b["err"].astype(np.int64)).max() <= 6

@@ -68,20 +68,22 @@ def test_mu_full_frame_vs_reference(engine, tag):
         check_user("mu K=8 %s frame" % tag, out, u, ref, g["mu_det_%s_u%d" % (tag, u)], g["mu_err_%s_u%d" % (tag, u)])
 
 
-def test_mu_single_user_loop_vs_oracle(engine):
+@pytest.mark.parametrize("tag", ["mrt", "zf"])
+def test_mu_single_user_loop_vs_oracle(engine, tag):
     """loop_single_user: oracle mu_frame(loop_single_user=True) is pinned bit-exact to the reference run of the script's
-    receivers (tests/golden/mu_su_loop.npz); the GPU path is compared with both"""
-    g, cfg, hl, tx_idx, real = mu_case("mrt")
+    receivers (tests/golden/mu_su_loop.npz), MU-MRT and - with the phase-only PA power the script ends up with - ZF; the GPU
+    path is compared with both"""
+    g, cfg, hl, tx_idx, real = mu_case(tag)
     gs = load_golden("mu_su_loop")
-    ref = lo.mu_frame(cfg, hl, tx_idx, None, 2, "mrt", loop_single_user=True, real=real)
+    ref = lo.mu_frame(cfg, hl, tx_idx, None, 2, tag, loop_single_user=True, real=real)
     engine.configure(n_ant=8, channel="injected", pa="softlim", ibo_db=2.0, receiver="mcnc")
     h = np.stack([hl[u][:, cfg.bins] for u in range(2)])[None]
-    out = engine.mu_simulate(1, 2, 300.0, precoding="mrt", loop_single_user=True,
+    out = engine.mu_simulate(1, 2, 300.0, precoding=tag, loop_single_user=True,
                              inject=dict(h=h, tx_idx=tx_idx[None], noise=np.zeros((1, 2, cfg.n_sub_carr), np.complex64)),
                              dumps=("det", "rx_eq"))
     for u in range(2):
         assert rel_l2(out["rx_eq"][0, u], ref["rx_eq"][u]) < 2 * TOL
-        check_user("mu K=8 mrt single-user loop", out, u, ref, gs["det_mrt_u%d" % u], gs["err_mrt_u%d" % u])
+        check_user("mu K=8 %s single-user loop" % tag, out, u, ref, gs["det_%s_u%d" % (tag, u)], gs["err_%s_u%d" % (tag, u)])
 
 
 def test_mu_device_rng_ber(engine):

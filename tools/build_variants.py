@@ -57,7 +57,11 @@ def time_variants(argv):
                 cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--steps", str(steps), "--warmup", "3", "--no-cpu"]
                 if frames:
                     cmd += ["--frames", frames]
-                res = subprocess.run(cmd, env=env, capture_output=True, text=True)
+                try:
+                    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=180)
+                except subprocess.TimeoutExpired:
+                    print(name, e, 'TIMEOUT (hung kernel?)', flush=True)
+                    continue
                 try:
                     d = json.loads(res.stdout.strip().splitlines()[-1])
                     print("%-22s %-28s round %d  kernel %.3f ms  step %.3f ms  %.1f k frames/s  e2e %.1f k  frac %.4f  ber5 %.5f"

@@ -61,4 +61,5 @@ res2 = cmu.receive([0, 2], y, other_usr_symbols=mod.modulate(bits, get_symbols_o
 llr = mod.soft_detection_llr(mod.modulate(bits, get_symbols_only=True)[0] + 0.1, noise_var=0.5)
 td = utilities.to_time_domain(x)
 fd = utilities.to_freq_domain(td, remove_cp=False)
-print("stage ops ok", utilities.count_mismatched_bits(res[0], bits[1]), len(res2), float(np.abs(fd - x).max()))
+f_psd, psd = utilities.welch(td.ravel(), fs=512, nfft=512, nperseg=128)
+print("stage ops ok", float(psd.sum()), utilities.count_mismatched_bits(res[0], bits[1]), len(res2), float(np.abs(fd - x).max()))
