@@ -276,7 +276,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     if (T64_RING) ring_acquire();
                     t64::exchange_store(x, buf, lane);
                     sy.x_sync();                // S2
-                    if (T64_RING >= 2) ring_release();   // token covers the stores only
+                    if (T64_RING >= 2) ring_release();   // token covers the stores only (passing it on earlier, after 32 or 48
+                                                         // of the 64 stores, measured slower)
                     if (T64_RING == 3) ring_acquire2();  // a second token for the loads
                     t64::pass2_load(x, buf, lane);
                     if (T64_RING == 1) ring_release();

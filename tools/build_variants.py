@@ -58,7 +58,7 @@ def time_variants(argv):
                 if frames:
                     cmd += ["--frames", frames]
                 try:
-                    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=180)
+                    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=75)
                 except subprocess.TimeoutExpired:
                     print(name, e, 'TIMEOUT (hung kernel?)', flush=True)
                     continue
