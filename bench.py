@@ -258,7 +258,7 @@ def run_gpu(a):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    stream = torch.cuda.Stream()
+    stream = torch.cuda.Stream(priority=-1)  # high priority: frame kernels before the library's background channel kernels
     torch.cuda.set_stream(stream)
 
     eng = LinkEngine(local)

@@ -90,7 +90,10 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         sscale_ready = !in.h_loop && !(rq->csi_eps > 0.0) && n >= 2 * c->n_sm && !los_closed_form;
         ca.sscale_out = sscale_ready ? c->sscale.as<float>() : nullptr;
         prof_begin(c, PROF_CHAN);
-        k_gen_channel<<<dim3(sscale_ready ? 1 : (K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), 256, 0, c->stream>>>(ca);
+        if (c->stream == c->prep_stream && !sscale_ready)  // pipelined: the light form that fits beside a frame-kernel CTA
+            k_gen_channel_bg<<<dim3((K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), CHAN_BG_THREADS, 0, c->stream>>>(ca);
+        else
+            k_gen_channel<<<dim3(sscale_ready ? 1 : (K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), 256, 0, c->stream>>>(ca);
         prof_end(c);
         c->launches++;
     } else if (cfg.channel_kind == MMIMO_CHAN_RAYLEIGH) {
@@ -177,6 +180,15 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     return 0;
 }
 
+// pipelined realisations: exchange the per-realisation buffers (and their events) with the second set
+static void swap_prep_set(mmimo_ctx* c) {
+    mmimo_ctx::PrepSet& a = c->alt;
+    std::swap(c->h_true, a.h_true); std::swap(c->h_loop, a.h_loop); std::swap(c->csi_nz, a.csi_nz);
+    std::swap(c->sscale, a.sscale); std::swap(c->agc_inv, a.agc_inv); std::swap(c->hkvk_inv, a.hkvk_inv);
+    std::swap(c->scal, a.scal); std::swap(c->alpha, a.alpha); std::swap(c->rx_pos, a.rx_pos);
+    std::swap(c->cur_ready, a.ready); std::swap(c->cur_released, a.released); std::swap(c->cur_used, a.used);
+}
+
 static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result* rs) {
     if (!c || !rq) return fail("mmimo_link: NULL argument");
     if (!c->configured) return fail("mmimo_link: context not configured (call mmimo_configure)");
@@ -214,6 +226,9 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         c->launches += 3;
     }
     unsigned long long* counters = c->counters.as<unsigned long long>();
+    // Pipelined realisations (asynchronous calls with device-generated channels): see mmimo_ctx::PrepSet
+    const bool pipelined = c->pipeline_prep && !rs && !rq->incl_clean_run && !rq->h_true && !rq->h_loop && !rq->csi_noise &&
+                           cfg.channel_kind != MMIMO_CHAN_INJECTED;
 
     for (size_t c0 = 0; c0 < (size_t)rq->n_frames; c0 += chunk) {
         const int n = (int)std::min<size_t>(chunk, (size_t)rq->n_frames - c0);
@@ -254,6 +269,14 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         if (rq->incl_clean_run == 2) continue;  // clean frames only
         // per-frame host inputs of this chunk: H2D on the copy stream into a staging slot (overlaps whatever the compute
         // stream is still running, normally the previous batch's frame kernel), permuted into place on the compute stream
+        if (pipelined) {  // the buffer set the previous batch's frame kernel is NOT reading
+            swap_prep_set(c);
+            if (c->h_true.reserve(hB) || c->sscale.reserve(chunk * N_SC * 4) || c->agc_inv.reserve(chunk * N_SC * 8) ||
+                c->hkvk_inv.reserve(chunk * N_SC * 8) || c->scal.reserve(chunk * sizeof(FrameScalars)) ||
+                c->alpha.reserve(chunk * K * 4) || c->rx_pos.reserve(chunk * 24))
+                return 1;
+            if (c->cur_used) CK(cudaStreamWaitEvent(c->prep_stream, c->cur_released, 0));
+        }
         mmimo_ctx::InSlot* sl = nullptr;
         if (rq->rx_pos || rq->tx_idx || rq->noise) {
             sl = &c->in_slot[c->slot_ctr++ & 1];
@@ -277,10 +300,21 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             }
             CK(cudaEventRecord(sl->copied, c->copy_stream));
             CK(cudaStreamWaitEvent(c->stream, sl->copied, 0));
+            if (pipelined) CK(cudaStreamWaitEvent(c->prep_stream, sl->copied, 0));
             sl->in_use = true;
         }
         RealisationIn in{(sl && rq->rx_pos) ? sl->pos.as<double>() : nullptr, rq->rx_pos, rq->h_true, rq->h_loop, rq->csi_noise, RNG_POS, RNG_RAYLEIGH, RNG_CSI};
-        if (run_realisation(c, rq, in, c0, n, &h_true, &h_loop, want_v)) return 1;
+        {
+            cudaStream_t main_stream = c->stream;
+            if (pipelined) c->stream = c->prep_stream;  // channel + realisation kernels of this batch beside the previous frame kernel
+            const int rc = run_realisation(c, rq, in, c0, n, &h_true, &h_loop, want_v);
+            c->stream = main_stream;
+            if (rc) return 1;
+            if (pipelined) {
+                CK(cudaEventRecord(c->cur_ready, c->prep_stream));
+                CK(cudaStreamWaitEvent(c->stream, c->cur_ready, 0));
+            }
+        }
 
         FrameArgs fa{};
         const long long hfs = (long long)K * N_SC;
@@ -340,6 +374,10 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         prof_end(c);
         c->launches++;
         CK(cudaGetLastError());
+        if (pipelined) {
+            CK(cudaEventRecord(c->cur_released, c->stream));
+            c->cur_used = true;
+        }
 
         if (rs) {  // optional per-frame dumps
             if (rs->det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->det + c0 * (I + 1) * N_SC, (size_t)n * (I + 1))) return 1;

@@ -86,6 +86,25 @@ struct mmimo_ctx {
     cudaStream_t copy_stream = nullptr;
     InSlot in_slot[2];
     unsigned slot_ctr = 0;
+    // Pipelined realisations (MMIMO_PIPELINE_PREP=1, off by default; mmimo_link_enqueue with device-generated channels): the
+    // per-realisation buffers exist twice; before every batch the members above are swapped with `alt` and the channel /
+    // realisation kernels of the batch run on prep_stream while the previous batch's frame kernel is still on the compute
+    // stream.  ready: the set has been filled (prep stream); released: the frame kernel that read the set has finished
+    // (compute stream).  Measured (profiles/r02_pipelined_prep.txt): results identical, but the light k_gen_channel_bg
+    // (64 threads, 56 registers, no shared memory, no barrier) is NOT scheduled beside resident frame-kernel CTAs although
+    // registers (4096 free), shared memory (10.6 KB free) and barriers would fit - with equal stream priorities it wins the
+    // race for the idle SMs and runs first, with a lower priority it waits for the frame kernel to end: 18.02-18.12 vs
+    // 18.13-18.18 ms per step, i.e. nothing worth twice the channel memory.
+    struct PrepSet {
+        DevBuf h_true, h_loop, csi_nz, sscale, agc_inv, hkvk_inv, scal, alpha, rx_pos;
+        cudaEvent_t ready = nullptr, released = nullptr;
+        bool used = false;
+    };
+    PrepSet alt;
+    cudaEvent_t cur_ready = nullptr, cur_released = nullptr;
+    bool cur_used = false;
+    cudaStream_t prep_stream = nullptr;
+    int pipeline_prep = 0;
     DevBuf counters;  // [0..63] distorted iterations, [64] clean
     // multi-point batch in flight (mmimo_link_sweep): device tables of 10^(x/10) per point, 64 counters per point
     struct Sweep { const double* snr_lin = nullptr; const double* ibo_lin = nullptr; int fpp = 0; unsigned long long* counters = nullptr; } sweep;
@@ -179,6 +198,7 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     c->n_sm = prop.multiProcessorCount;
     if (const char* fk = getenv("MMIMO_FRAME_KERNEL")) c->frame_kernel = !strcmp(fk, "r64") ? 1 : !strcmp(fk, "r16") ? 2 : 0;
     if (const char* e = getenv("MMIMO_PREP_ANALYTIC")) c->prep_analytic = atoi(e) != 0;
+    if (const char* e = getenv("MMIMO_PIPELINE_PREP")) c->pipeline_prep = atoi(e) != 0;
     if (const char* e = getenv("MMIMO_T64_STAGGER")) c->t64_stagger = std::max(0, atoi(e));
     if (const char* e = getenv("MMIMO_CTAS_PER_SM")) c->ctas_per_sm_r16 = std::min(8, std::max(1, atoi(e)));
     const int rc = create_body(c);
@@ -189,9 +209,18 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
 
 // everything of mmimo_create that can fail after the context exists (the caller destroys it on failure)
 static int create_body(mmimo_ctx* c) {
-    CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    // The compute stream gets the highest priority, the prep stream the lowest: when the frame kernel of batch n and the
+    // background channel kernel of batch n + 1 become eligible together, the block scheduler must place the 148 frame CTAs
+    // (one whole SM each) first and let the light channel blocks fill what is left - the other way round the frame kernel
+    // would wait for the channel kernel to drain.  A caller-supplied stream (mmimo_set_stream) should be a high-priority one.
+    int prio_least = 0, prio_greatest = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    CK(cudaStreamCreateWithPriority(&c->own_stream, cudaStreamNonBlocking, prio_greatest));
     c->stream = c->own_stream;
-    CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithPriority(&c->copy_stream, cudaStreamNonBlocking, prio_least));
+    CK(cudaStreamCreateWithPriority(&c->prep_stream, cudaStreamNonBlocking, prio_least));
+    for (cudaEvent_t* e : {&c->cur_ready, &c->cur_released, &c->alt.ready, &c->alt.released})
+        CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     for (auto& sl : c->in_slot) {
         CK(cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&sl.consumed, cudaEventDisableTiming));
@@ -235,6 +264,9 @@ static int create_body(mmimo_ctx* c) {
     CK(cudaFuncSetAttribute(k_link_frame<PA_SOFT_LIMITER, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame<PA_RAPP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame<PA_TOI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_SMEM_BYTES_MU));
+    // the background channel kernel runs beside resident frame-kernel CTAs: it must ask for the same (maximal) shared-memory
+    // carve-out, or the SM would have to be reconfigured and the two kernels could not share it
+    CK(cudaFuncSetAttribute(k_gen_channel_bg, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if (stage_kernels_init()) return 1;
     return 0;
 }
@@ -244,6 +276,7 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    if (c->prep_stream) cudaStreamSynchronize(c->prep_stream);
     for (auto& r : c->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     c->prof_recs.clear();
     for (auto& sl : c->in_slot) {
@@ -252,6 +285,12 @@ extern "C" void mmimo_destroy(mmimo_ctx* c) {
         if (sl.consumed) cudaEventDestroy(sl.consumed);
     }
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->prep_stream) { cudaStreamSynchronize(c->prep_stream); cudaStreamDestroy(c->prep_stream); }
+    for (DevBuf* b : {&c->alt.h_true, &c->alt.h_loop, &c->alt.csi_nz, &c->alt.sscale, &c->alt.agc_inv, &c->alt.hkvk_inv, &c->alt.scal,
+                      &c->alt.alpha, &c->alt.rx_pos})
+        b->release();
+    for (cudaEvent_t e : {c->cur_ready, c->cur_released, c->alt.ready, c->alt.released})
+        if (e) cudaEventDestroy(e);
     DevBuf* all[] = {&c->tw4096, &c->tw256, &c->tw_t64, &c->sweep_tab, &c->sweep_cnt, &c->freq_slot, &c->freq_bin, &c->tx_pos, &c->h_true, &c->h_loop, &c->csi_nz, &c->rxeq_scr, &c->v, &c->sscale, &c->agc_inv,
                      &c->hkvk_inv, &c->scal, &c->alpha, &c->rx_pos, &c->tx_idx, &c->noise, &c->det, &c->err,
                      &c->rx_eq, &c->corr, &c->stage, &c->cnc_ones, &c->cnc_v, &c->cnc_agc_inv, &c->counters,

@@ -143,6 +143,65 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
     }
 }
 
+// k_gen_channel_bg: the same rows as k_gen_channel's (K/8, F) form, written by 64-thread CTAs that need 64 registers per
+// thread and 200 bytes of shared memory - small enough to be resident NEXT TO a CTA of the frame kernel (240 registers x 256
+// threads, 221.5 KB), so that the channel rows of batch n + 1 are generated in the issue slots the frame kernel of batch n
+// leaves idle (link_host.inl, "pipelined realisations").  Same arithmetic, same operation order per element: bit-identical rows.
+constexpr int CHAN_BG_THREADS = 64;
+// no shared memory and no barrier: every thread derives the receiver position and the geometry of the CTA's antennas itself
+__global__ void __launch_bounds__(CHAN_BG_THREADS, 16) k_gen_channel_bg(const ChanArgs a) {
+    const int kb = blockIdx.x * CHAN_ANT_PER_CTA, f = blockIdx.y, t = threadIdx.x;
+    double rx[3];
+    if (a.rx_pos_in) {
+        rx[0] = a.rx_pos_in[f * 3 + 0]; rx[1] = a.rx_pos_in[f * 3 + 1]; rx[2] = a.rx_pos_in[f * 3 + 2];
+    } else {
+        uint32_t r[4];
+        const uint64_t fid = a.frame_id0 + f;
+        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.pos_stream, 0u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+        if (a.rx0_tab) {
+            const double* n0 = a.rx0_tab + (size_t)((a.frame_id0 + f) % (uint64_t)a.n_usr) * 3;
+            rx[0] = n0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+            rx[1] = n0[1] + (u01(r[2], r[3]) - 0.5) * a.loc_var;
+            rx[2] = n0[2];
+        } else {
+            rx[0] = a.rx0[0] + (u01(r[0], r[1]) - 0.5) * a.loc_var;
+            rx[1] = a.rx0[0] + (u01(r[2], r[3]) - 0.5) * a.loc_var;  // quirk: rx_loc_x, mp_model.py:146,196
+            rx[2] = a.rx0[2];
+        }
+    }
+    if (a.rx_pos_out && kb == 0 && t == 0) { a.rx_pos_out[f * 3 + 0] = rx[0]; a.rx_pos_out[f * 3 + 1] = rx[1]; a.rx_pos_out[f * 3 + 2] = rx[2]; }
+    const int nk = min(CHAN_ANT_PER_CTA, a.n_ant - kb);
+    for (int i = 0; i < nk; ++i) {
+        const int k = kb + i;  // geometry of antenna k, exactly as in k_gen_channel (channel.py:56-66, :118-140)
+        const double dx = a.tx_pos[k * 3 + 0] - rx[0], dy = a.tx_pos[k * 3 + 1] - rx[1], dz = a.tx_pos[k * 3 + 2] - rx[2];
+        const double d1 = sqrt(dx * dx + dy * dy + dz * dz);
+        double d2 = 0.0;
+        if (a.kind == 1) {
+            const double dxy = sqrt(dx * dx + dy * dy);
+            const double el = atan((a.tx_pos[k * 3 + 2] + rx[2]) / dxy);
+            const double sn = sin(el);
+            d2 = a.tx_pos[k * 3 + 2] / sn + rx[2] / sn;
+        }
+        const double amp0 = a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846);
+        const double t1 = d1 * (1.0 / C_LIGHT), t2 = d2 * (1.0 / C_LIGHT);
+        const float amp1 = (float)(amp0 / d1), amp2 = a.kind == 1 ? (float)(amp0 / d2) : 0.f;
+        float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+#pragma unroll 2
+        for (int p = 2 * t; p < N_SC; p += 2 * CHAN_BG_THREADS) {
+            const double2 fr = *reinterpret_cast<const double2*>(a.freq_slot + p);
+            float2 h0 = path_coeff(t1, fr.x, amp1, a.skip_attenuation);
+            float2 h1 = path_coeff(t1, fr.y, amp1, a.skip_attenuation);
+            if (a.kind == 1) {
+                const float2 g0 = path_coeff(t2, fr.x, amp2, a.skip_attenuation);
+                const float2 g1 = path_coeff(t2, fr.y, amp2, a.skip_attenuation);
+                h0.x -= g0.x; h0.y -= g0.y;
+                h1.x -= g1.x; h1.y -= g1.y;
+            }
+            *reinterpret_cast<float4*>(out + p) = make_float4(h0.x, h0.y, h1.x, h1.y);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // k_prep_realisation: AntennaArray.set_precoding_matrix(MRT) (antenna_array.py:163-171),
 // AntennaArray.update_distortion (:313-360) and Link.recalculate_agc (mp_model.py:290-329) for one
