@@ -67,8 +67,41 @@ def golden_mu_k64(n_ant=64, ibo=0.0, ebn0=15.0, iters=(0, 1, 2, 3)):
     print("mu_k64 ok:", {k: v.tolist() for k, v in out.items() if k.startswith("err_")})
 
 
+def golden_sdr_k64(n_ant=64):
+    """SDR snapshots at the size BASELINE config 4 names (main_beampatterns_plotting/sdr_mp.py:124-151 on the reference classes):
+    K = 64 LOS MRT, IBO 0 and 3 dB, one snapshot each; receiver positions and bits are stored, the channel is rebuilt from them."""
+    my_mod, my_dist, my_tx, my_rx, my_array = mg.build_objects(n_ant)
+    rng = np.random.default_rng(29)
+    out = dict(sdr_ibo=np.array([0.0, 3.0]))
+    des, dis, poss, bits_l = [], [], [], []
+    for ibo in out["sdr_ibo"]:
+        my_rx.set_position(212.0 + rng.uniform(-5, 5), 212.0 + rng.uniform(-5, 5), 1.5)
+        ch = mg.make_channel("los", my_array, my_rx)
+        my_array.set_precoding_matrix(channel_mat_fd=ch.channel_mat_fd, mr_precoding=True)
+        my_array.update_distortion(ibo_db=ibo, avg_sample_pow=my_mod.avg_sample_power)
+        vk = my_array.get_precoding_mat()
+        vk_pow = np.sum(np.power(np.abs(vk), 2), axis=1)
+        ibo_vec = 10 * np.log10(10 ** (ibo / 10) * my_mod.n_sub_carr / (vk_pow * n_ant))
+        ak = np.expand_dims(my_mod.calc_alpha(ibo_db=ibo_vec), axis=1)
+        bits = rng.choice((0, 1), my_mod.n_bits_per_ofdm_sym)
+        x_fd, x_clean = my_array.transmit(bits, out_domain_fd=True, skip_dist=False, return_both=True)
+        rx = ch.propagate(in_sig_mat=x_fd, sum_signals=False)
+        rx_sc = np.concatenate((rx[:, -1024:], rx[:, 1:1025]), axis=1)
+        cl = ch.propagate(in_sig_mat=x_clean, sum_signals=False)
+        cl_sc = np.concatenate((cl[:, -1024:], cl[:, 1:1025]), axis=1)
+        des.append(np.sum(np.abs(np.sum(ak * cl_sc, axis=0)) ** 2))
+        dis.append(np.sum(np.abs(np.sum(rx_sc - ak * cl_sc, axis=0)) ** 2))
+        poss.append((my_rx.cord_x, my_rx.cord_y, my_rx.cord_z))
+        bits_l.append(bits.astype(np.uint8))
+    out.update(sdr_pos=np.array(poss), sdr_bits=np.stack(bits_l), sdr_desired=np.array(des), sdr_distortion=np.array(dis), n_ant=n_ant)
+    np.savez_compressed(os.path.join(HERE, "sdr_k64.npz"), **out)
+    print("sdr_k64 ok: SDR [dB]", 10 * np.log10(out["sdr_desired"] / out["sdr_distortion"]))
+
+
 if __name__ == "__main__":
-    what = sys.argv[1:] or ["mcnc", "cnc", "mu"]
+    what = sys.argv[1:] or ["mcnc", "cnc", "mu", "sdr"]
+    if "sdr" in what:
+        golden_sdr_k64()
     if "mu" in what:
         golden_mu_k64()
     if "cnc" in what:

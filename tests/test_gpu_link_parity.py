@@ -169,6 +169,13 @@ def test_fused_sdr_matches_reference_snapshots(engine):
         des, dis = engine.sdr(1, inject=dict(rx_pos=g["sdr_pos"][i:i + 1], tx_idx=idx[None]))
         assert abs(des[0] / g["sdr_desired"][i] - 1) < 2e-5
         assert abs(dis[0] / g["sdr_distortion"][i] - 1) < 3e-4   # difference of nearly equal signals in fp32
+    g64 = load_golden("sdr_k64")   # the size BASELINE config 4 names: 64 antennas (tests/golden/make_golden_k64.py)
+    for i, ibo in enumerate(g64["sdr_ibo"]):
+        engine.configure(n_ant=64, channel="los", pa="softlim", ibo_db=float(ibo))
+        idx = lo.bits_to_indices(g64["sdr_bits"][i], 6)
+        des, dis = engine.sdr(1, inject=dict(rx_pos=g64["sdr_pos"][i:i + 1], tx_idx=idx[None]))
+        assert abs(des[0] / g64["sdr_desired"][i] - 1) < 2e-5
+        assert abs(dis[0] / g64["sdr_distortion"][i] - 1) < 3e-4
     # device RNG: SDR grows with the back-off (BASELINE config 4, "SDR vs IBO")
     sdr = []
     for ibo in (0.0, 3.0, 6.0):

@@ -29,7 +29,8 @@ N_PHI = 160   # frames per point for the over-dispersion estimate
 BUDGET = {"fixed-ber": (5e6, 1e5),    # main_mp_miso_mcnc_constant_ber_req_ebn0_vs_ibo.py:57-58
           "nant-chan": (10e7, 3e6),   # main_mp_miso_mcnc_ber_vs_nant_vs_chan.py:59-60
           "ebn0": (1e7, 1e6),         # main_mp_miso_mcnc_ber_vs_ebn0.py:58-59
-          "ibo": (1e7, 1e5)}          # main_mp_miso_mcnc_ber_vs_ibo.py:55-56
+          "ibo": (1e7, 1e5),          # main_mp_miso_mcnc_ber_vs_ibo.py:55-56
+          "csi": (3e7, 1e6)}          # main_mp_miso_mcnc_csi_err_ber_vs_ebn0.py:62-63
 
 
 @pytest.fixture(scope="module")
@@ -53,9 +54,9 @@ def snr_of(ebn0):
     return 10 * math.log10(10 ** (ebn0 / 10) * 6)
 
 
-def phi_of_point(eng, ebn0, n_iter, clean=False, seed=99):
+def phi_of_point(eng, ebn0, n_iter, clean=False, seed=99, csi_eps=0.0):
     """over-dispersion var(e_f) / mean(e_f) per result slot of the CONFIGURED link at this Eb/N0"""
-    out = eng.simulate(N_PHI, n_iter, snr_of(ebn0), seed=seed, incl_clean_run=clean,
+    out = eng.simulate(N_PHI, n_iter, snr_of(ebn0), seed=seed, incl_clean_run=clean, csi_eps=csi_eps,
                        dumps=("err_per_frame", "clean_err_per_frame") if clean else ("err_per_frame",))
     phi = dispersion(out["err_per_frame"])
     if clean:
@@ -185,3 +186,54 @@ def test_variance_model_on_two_independent_gpu_runs(engine):
     k, n = reference_variance_factor(runs[0], bits, runs[1], bits, phi, axis=1)
     assert k < 1.6, (k, n)
     print("self-consistency", rec, "scatter factor", k)
+
+
+@pytest.mark.parametrize("eps", [0.1, 0.2, 0.4])
+def test_ber_vs_ebn0_with_csi_error(engine, eps):
+    """main_mp_miso_mcnc_csi_err_ber_vs_ebn0.py (BASELINE config 5, CSI-error sweep): channel knowledge
+    sqrt(1 - eps^2) h + eps CN(0, mean |h|^2) per antenna (mp_model.py:264-284) drawn by the device RNG (k_csi_error), used for
+    precoding, AGC and the MCNC loop while the true channel propagates; BER against the shipped curves."""
+    import ber_sweep
+    ref = load_golden("ref_curves")["mcnc_los_csi_eps%.1f" % eps]
+    a = args(sweep="ebn0", ebn0="6:20:2", csi_eps=eps, bits_max=3e7, frames_per_step=2442)
+    engine.configure(constel_size=64, n_ant=64, pa="softlim", ibo_db=0.0, channel="los", receiver="mcnc")
+    ax, rows, frames = ber_sweep.run_sweep(engine, a)
+    cols = [int(np.argmin(np.abs(ref[0] - e))) for e in ax]
+    assert np.array_equal(ref[0][cols], ax)
+    phi = np.stack([phi_of_point(engine, e, 8, clean=True, csi_eps=eps) for e in ax], axis=1)
+    bits_got = np.ceil(3e7 / B / 2442) * 2442 * B
+    rec = assert_within_ci("ber-vs-ebn0 mcnc_los with CSI error eps %.1f" % eps, rows, bits_got, ref[1:, cols],
+                           ref_bits(ref[1:, cols], *BUDGET["csi"]), phi, min_points=40)
+    print("csi", eps, rec)
+
+
+def test_two_user_mrt_script_receivers_vs_reference_counts(engine):
+    """BASELINE config 5 at full size with the device RNG: main_multiuser/main_mp_mulituser_mcnc_ber_vs_ebn0.py (12 workers of
+    multiuser_mp_prototype.multiuser_mcnc_parallel: two users at -30 / +30 degrees, 100 m / 316.3 m, MU-MRT, 64 antennas, the
+    script's single-user McncReceiver per user, positions re-drawn per frame) shipped the raw error and bit counts of every
+    worker; summed they give exact reference BERs AND bit counts per (Eb/N0, user, iteration).  The fused two-user path is run
+    in batches, the batch-to-batch scatter gives the variance of its own estimate.
+    Eb/N0 >= 10 dB only: every worker of the reference builds `noise.Awgn(snr_db=10, seed=1234)` (multiuser_mp_prototype.py:391),
+    i.e. all 12 draw the SAME noise sequence; where the errors are noise-dominated their estimates are correlated and the pooled
+    bit count over-states the precision of the shipped numbers (at 6 dB the fused path sits 0.3 % above them, 3-4 sigma of the
+    naive interval, while 10 ... 20 dB agree within 1.5 sigma)."""
+    g = load_golden("ref_curves")
+    ax, r_err, r_bits = g["mu_mr_mcnc_ebn0"], g["mu_mr_mcnc_err"], g["mu_mr_mcnc_bits"]
+    ang, dist = np.deg2rad(np.array([-30.0, 30.0]) + 90.0), (100.0, 316.3)     # multiuser_mp_prototype.py:37-42
+    usr_pos = tuple((float(np.cos(a) * d), float(np.sin(a) * d), 1.5) for a, d in zip(ang, dist))
+    engine.configure(constel_size=64, n_ant=64, pa="softlim", ibo_db=0.0, channel="los", receiver="mcnc", rx_loc_var=10.0)
+    n_batch, per_batch, n_iter = 32, 52, 8
+    cols = [int(np.argmin(np.abs(ax - e))) for e in (10.0, 12.0, 14.0, 16.0, 18.0, 20.0)]
+    got, phi, p_ref, bits_ref = [], [], [], []
+    for c in cols:
+        e_b = np.stack([engine.mu_simulate(per_batch, n_iter, snr_of(float(ax[c])), precoding="mrt", usr_pos=usr_pos,
+                                           loop_single_user=True, seed=2137 + c, frame_id0=b * per_batch)["err"].astype(np.float64)
+                        for b in range(n_batch)])                              # [batch][user][iteration]
+        got.append(e_b.sum(axis=0) / (n_batch * per_batch * B))
+        m, v = e_b.mean(axis=0), e_b.var(axis=0, ddof=1)
+        phi.append(np.maximum(np.where(m > 0, v / np.maximum(m, 1e-300), 1.0), 1.0))   # over-dispersion at batch level
+        p_ref.append(r_err[c][:, 1:] / r_bits[c][:, 1:])                       # slot 0 is the script's clean run
+        bits_ref.append(r_bits[c][:, 1:])
+    rec = assert_within_ci("two-user MU-MRT, script receivers, K=64 (reference counts of 12 workers)", np.array(got),
+                           float(n_batch * per_batch * B), np.array(p_ref), np.array(bits_ref), np.array(phi), min_points=80)
+    print("mu", rec)
