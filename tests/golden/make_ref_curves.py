@@ -24,6 +24,9 @@ RAGGED = {
 }
 for _eps in (0.1, 0.2, 0.4):  # main_mp_miso_mcnc_csi_err_ber_vs_ebn0.py (BASELINE config 5, CSI-error sweep)
     FILES["mcnc_los_csi_eps%.1f" % _eps] = ("ber_vs_ebn0_mcnc_los_csi_eps%.3f_nant64_ibo0_ebn0_min5_max20_step0.50_niter1_2_3_4_5_6_7_8.csv" % _eps)
+for _tag in ("mr", "zf"):  # main_multiuser/main_multiuser_cnc_ber_vs_ebn0.py: two users, CncReceiver; axis + 2 x (clean + 9 iterations)
+    FILES["mu_%s_cnc" % _tag] = ("ber_vs_ebn0_mu_%s_cnc_los_nant64_ibo0_ebn0_min5_max20_step1.00_niter1_2_3_4_5_6_7_8_angles-30_30_"
+                                 "distances100_316.3.csv" % _tag)
 FILES["ber_vs_nant_mcnc"] = "ber_vs_nant_mcnc_nant1_2_4_8_16_32_64_128_ebn0_15_ibo0_niter1_2_3_4_5_6_7_8.csv"
 out = {}
 for key, (fn, ebn0) in RAGGED.items():

@@ -237,3 +237,37 @@ def test_two_user_mrt_script_receivers_vs_reference_counts(engine):
     rec = assert_within_ci("two-user MU-MRT, script receivers, K=64 (reference counts of 12 workers)", np.array(got),
                            float(n_batch * per_batch * B), np.array(p_ref), np.array(bits_ref), np.array(phi), min_points=80)
     print("mu", rec)
+
+
+@pytest.mark.parametrize("tag,precoding", [("mr", "mrt"), ("zf", "zf")])
+def test_two_user_cnc_receivers_vs_reference_curves(engine, tag, precoding):
+    """main_multiuser/main_multiuser_cnc_ber_vs_ebn0.py: two users (same geometry as above), MU-MRT or zero forcing, the
+    single-antenna CncReceiver per user, shipped as ber_vs_ebn0_mu_{mr,zf}_cnc_los_nant64_...csv (axis + per user: no distortion
+    + iterations 0..8).  Both files are about ten times noisier than the script's present budget (bits_sent_max 1e7 /
+    n_err_min 1e6, :67-68) implies - their point-to-point scatter along the 16 Eb/N0 points says so, e.g. the interfered
+    user's BER of 0.23 jumps by 1 % between neighbouring points - so their noise level is taken from that scatter
+    (ci_util.reference_variance_factor), as for the fixed-BER grid."""
+    ref = load_golden("ref_curves")["mu_%s_cnc" % tag]
+    assert ref.shape == (21, 16)
+    ax = ref[0]
+    p_ref = np.transpose(np.stack([ref[2:11], ref[12:21]]), (2, 0, 1))          # [ebn0][user][iteration 0..8]
+    ang, dist = np.deg2rad(np.array([-30.0, 30.0]) + 90.0), (100.0, 316.3)
+    usr_pos = tuple((float(np.cos(a) * d), float(np.sin(a) * d), 1.5) for a, d in zip(ang, dist))
+    engine.configure(constel_size=64, n_ant=64, pa="softlim", ibo_db=0.0, channel="los", receiver="mcnc", rx_loc_var=10.0)
+    n_batch, per_batch, n_iter = 24, 52, 8
+    got, phi = [], []
+    for c, e in enumerate(ax):
+        e_b = np.stack([engine.mu_simulate(per_batch, n_iter, snr_of(float(e)), precoding=precoding, usr_pos=usr_pos,
+                                           receiver="cnc", seed=977 + c, frame_id0=b * per_batch)["err"].astype(np.float64)
+                        for b in range(n_batch)])
+        got.append(e_b.sum(axis=0) / (n_batch * per_batch * B))
+        m, v = e_b.mean(axis=0), e_b.var(axis=0, ddof=1)
+        phi.append(np.maximum(np.where(m > 0, v / np.maximum(m, 1e-300), 1.0), 1.0))
+    got, phi = np.array(got), np.array(phi)
+    bits_got = float(n_batch * per_batch * B)
+    bits_ref = ref_bits(p_ref, 1e7, 1e6)
+    k_ref, n_k = reference_variance_factor(got, bits_got, p_ref, bits_ref, phi, axis=0)
+    assert n_k > 150 and k_ref < 16.0, (k_ref, n_k)
+    rec = assert_within_ci("two-user %s, CncReceiver, K=64, 16 Eb/N0 points" % precoding, got, bits_got, p_ref, bits_ref, phi,
+                           min_points=200, ref_var_factor=k_ref)
+    print("mu cnc", tag, rec)
