@@ -205,34 +205,52 @@ def test_multi_point_sweep_equals_point_by_point(engine):
     assert np.array_equal(e2[0], r0)
 
 
-def test_radix64_and_radix16_frame_kernels_agree(engine, monkeypatch):
-    """The default frame kernel (two-pass radix-64, frame_kernel_r64.cuh) and the three-pass radix-16 kernel
-    (frame_kernel.cuh, MMIMO_FRAME_KERNEL=r16) are two decompositions of the same frame: equalised samples agree to
-    fp32 rounding, detections differ only on decision boundaries, and each kernel is bit-reproducible run to run (the
-    four antenna groups of the radix-64 kernel are summed in a fixed order)."""
-    # antenna counts that leave groups of the radix-64 kernel idle or ragged (1, 5, 6) included
-    for pa, n_ant, rx in (("softlim", 16, "mcnc"), ("rapp", 6, "mcnc"), ("softlim", 8, "cnc"), ("toi", 4, "mcnc"),
-                          ("softlim", 1, "mcnc"), ("softlim", 5, "cnc"), ("none", 3, "mcnc")):
-        engine.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=1.0, receiver=rx)
-        outs = {}
-        for kern in ("r64", "r16"):
-            monkeypatch.setenv("MMIMO_FRAME_KERNEL", kern)
-            outs[kern] = engine.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
-            again = engine.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
-            assert np.array_equal(outs[kern]["err"], again["err"]) and np.array_equal(outs[kern]["rx_eq"], again["rx_eq"])
-        monkeypatch.delenv("MMIMO_FRAME_KERNEL")
-        a, b = outs["r64"], outs["r16"]
-        rel = np.linalg.norm(a["rx_eq"] - b["rx_eq"]) / np.linalg.norm(b["rx_eq"])
-        assert rel < 2e-6, (pa, rel)
-        assert (a["det"] != b["det"]).mean() < 1e-3, pa
-        assert np.abs(a["err"].astype(np.int64) - b["err"].astype(np.int64)).max() <= 6, (a["err"], b["err"])
+def test_radix64_and_radix16_frame_kernels_agree(monkeypatch):
+    """The three forms of the frame kernel - the default scaled-tangent radix-64 kernel with its exchange token ring
+    (frame_kernel_t64.cuh), the round-1 radix-64 kernel (MMIMO_FRAME_KERNEL=r64) and the three-pass radix-16 kernel (=r16) -
+    are decompositions of the same frame: equalised samples agree to fp32 rounding, detections differ only on decision
+    boundaries, and each kernel is bit-reproducible run to run (the four antenna groups are summed in a fixed order).
+    The kernel form is read once per context (mmimo_create), hence one engine per form."""
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    engines = {}
+    try:
+        for kern in ("t64", "r64", "r16"):
+            if kern == "t64":
+                monkeypatch.delenv("MMIMO_FRAME_KERNEL", raising=False)
+            else:
+                monkeypatch.setenv("MMIMO_FRAME_KERNEL", kern)
+            engines[kern] = LinkEngine(0)
+        monkeypatch.delenv("MMIMO_FRAME_KERNEL", raising=False)
+        # antenna counts that leave groups of the radix-64 kernels idle or ragged (1, 3, 5, 6) included: the token ring must
+        # still be passed on by groups that have no antenna in a round
+        for pa, n_ant, rx in (("softlim", 16, "mcnc"), ("rapp", 6, "mcnc"), ("softlim", 8, "cnc"), ("toi", 4, "mcnc"),
+                              ("softlim", 1, "mcnc"), ("softlim", 5, "cnc"), ("none", 3, "mcnc"), ("softlim", 7, "mcnc")):
+            outs = {}
+            for kern, eng in engines.items():
+                eng.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=1.0, receiver=rx)
+                outs[kern] = eng.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
+                again = eng.simulate(12, 3, 17.0, seed=31, dumps=("rx_eq", "det"))
+                assert np.array_equal(outs[kern]["err"], again["err"]) and np.array_equal(outs[kern]["rx_eq"], again["rx_eq"])
+            b = outs["r16"]
+            for kern in ("t64", "r64"):
+                a = outs[kern]
+                rel = np.linalg.norm(a["rx_eq"] - b["rx_eq"]) / np.linalg.norm(b["rx_eq"])
+                assert rel < 2e-6, (kern, pa, rel)
+                assert (a["det"] != b["det"]).mean() < 1e-3, (kern, pa)
+                assert np.abs(a["err"].astype(np.int64) - b["err"].astype(np.int64)).max() <= 6, (kern, a["err"], b["err"])
+            # the three forms are really three kernels: their samples differ in the last bits
+            assert not np.array_equal(outs["t64"]["rx_eq"], outs["r16"]["rx_eq"]) or pa == "none"
+    finally:
+        for eng in engines.values():
+            eng.close()
 
 
 def test_fused_norm_pass_is_bit_identical(engine):
     """From 2 realisations per SM on, k_gen_channel writes the MRT symbol scale itself (one CTA per realisation) and
     k_prep_realisation skips its norm pass; below that the realisation kernel computes it.  Same operation order, so a
-    large batch and the same frames run as small batches give exactly the same counters and samples."""
-    engine.configure(n_ant=16, channel="los", pa="softlim", ibo_db=0.0, receiver="mcnc")
+    large batch and the same frames run as small batches give exactly the same counters and samples.  (Two-path channel: a
+    line-of-sight channel goes through the closed-form k_prep_los at every batch size.)"""
+    engine.configure(n_ant=16, channel="two_path", pa="softlim", ibo_db=0.0, receiver="mcnc")
     n, n_iter = 320, 2                      # 320 >= 2 * 148: fused path
     big = engine.simulate(n, n_iter, 16.0, seed=9, frame_id0=500, dumps=("rx_eq",))
     err = np.zeros_like(big["err"])
