@@ -38,6 +38,9 @@ namespace mmimo {
 #define T64_RING 2  // the groups take turns in the shared-memory exchange (token ring over named barriers): 1 stores + loads,
                    // 2 stores only (measured best), 3 one token for the stores and one for the loads; 0 off
 #endif
+#ifndef T64_EPI_EARLY
+#define T64_EPI_EARLY 1  // the AGC row of the pass epilogue is loaded before the antenna groups meet (L2 latency under the barriers)
+#endif
 #ifndef T64_PA_UNIT
 #define T64_PA_UNIT 1  // PA evaluated on the signal scaled to a unit threshold (one multiply less per sample)
 #endif
@@ -322,6 +325,12 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                     for (int i = 0; i < T64_ACC_SMEM; ++i) accx_s[i * FFT_THREADS] = av[i];
                 }
             }
+            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
+            float2 aiv[8];
+            if (T64_EPI_EARLY) {
+#pragma unroll
+                for (int jp = 0; jp < 8; ++jp) aiv[jp] = ai[jp * 256 + t];
+            }
             if (T64_RING) {  // groups with one chain less than the others still pass the token on
                 const int mine = K > g ? (K - g + R64_GROUPS - 1) / R64_GROUPS : 0, slots = (K + R64_GROUPS - 1) / R64_GROUPS;
                 for (int e = 2 * mine; e < 2 * slots; ++e) {
@@ -342,14 +351,13 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                 if (T64_PA_UNIT) accn[jp] = pmul(accn[jp], pbc(pa_out_scale));
             }
 
-            const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs;
             if (!MU && a.sdr_desired) {  // ---- signal-to-distortion snapshot instead of the receiver (FrameArgs) ----
                 double pd = 0.0, pi = 0.0;
 #pragma unroll
                 for (int jp = 0; jp < 8; ++jp) {
                     const int p = jp * 256 + t;
                     const float2 ac = unpk(accn[jp]);            // 64 x the noise-free received signal
-                    const float2 iv = ai[p];                     // 1 / (64 agc)
+                    const float2 iv = T64_EPI_EARLY ? aiv[jp] : ai[p];                   // 1 / (64 agc)
                     const float m = 1.0f / (64.0f * (iv.x * iv.x + iv.y * iv.y));
                     const float2 agc = make_float2(iv.x * m, -iv.y * m);
                     const float2 des = cmul(qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu), agc);
@@ -407,12 +415,12 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                         corr = a.rx_eq_in[(size_t)f * N_SC + p];
                     } else {
                         const float2 r = make_float2(fmaf(64.f, nz[jp].x, ac.x), fmaf(64.f, nz[jp].y, ac.y));
-                        corr = cmul(r, ai[p]);
+                        corr = cmul(r, T64_EPI_EARLY ? aiv[jp] : ai[p]);
                     }
                     rxeq_s[p] = corr;
                     if (a.rx_eq_out) a.rx_eq_out[(size_t)f * N_SC + p] = corr;
                 } else {
-                    const float2 z = cmul(ac, ai[p]);
+                    const float2 z = cmul(ac, T64_EPI_EARLY ? aiv[jp] : ai[p]);
                     const float2 sy0 = qam_symbol(a.qam, (curw[jp >> 2] >> (8 * (jp & 3))) & 0xffu);
                     const float2 d = csub(z, sy0);   // distortion estimate, corrector.py:205
                     corr = csub(rxeq_s[p], d);       // corrector.py:184
