@@ -246,6 +246,23 @@ int mmimo_fft(mmimo_ctx* ctx, int inverse, int n, int rows, int skip, int cp, co
  * scripts).  x: n complex samples; psd [nfft] doubles in FFT-bin order, freqs [nfft] = fftfreq(nfft, 1 / fs) (may be NULL).
  * nfft a power of two in 8..8192, nperseg <= nfft. */
 int mmimo_welch_psd(mmimo_ctx* ctx, size_t n, const float* x, int nperseg, int nfft, double fs, double* freqs, double* psd);
+/* NO COUNTERPART IN THE REFERENCE - added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as mmimo_welch_psd
+ * (same kernels except that every nfft goes through the table-free transform), but the entry point allocates nothing and
+ * needs no context: no cudaMalloc / cudaFree / allocating library routine is called.  Its scratch (windowed segments, their
+ * spectra, the fp64 accumulator) is one file-scope `static __device__` array of 2 * MMIMO_WELCH_NOALLOC_MAX_ELEMS * 8 + 65536
+ * bytes (8.06 MiB) that every GPU which loads the library holds until the process exits.
+ *   x_dev   : n complex64 samples, DEVICE memory of the CURRENT device (cudaSetDevice is the caller's business);
+ *   psd_dev : [nfft] doubles, DEVICE memory, FFT-bin order (frequencies: fftfreq(nfft, 1 / fs), not returned);
+ *   stream  : cudaStream_t the work is enqueued on (NULL = default stream); the call does NOT synchronise.
+ * Limit: n_seg * nfft <= MMIMO_WELCH_NOALLOC_MAX_ELEMS with n_seg = (n - nperseg / 2) / (nperseg - nperseg / 2); beyond it the
+ * call fails (returns 1, mmimo_last_error() names the limit) and nothing is launched.  nfft a power of two in 8..8192,
+ * nperseg <= nfft.  All calls share the one array, which keeps the last call's contents (the accumulator is cleared on the
+ * stream at the start of every call): calls that OVERLAP on one GPU - two streams, two host threads - race; serialise them.
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress) and opts the transform into its shared
+ * memory size; make that first call outside stream capture. */
+#define MMIMO_WELCH_NOALLOC_MAX_ELEMS ((size_t)1 << 19)
+int mmimo_welch_psd_noalloc(size_t n, const float* x_dev, int nperseg, int nfft, double fs, double* psd_dev, void* stream);
 /* SoftLimiter/Rapp/ThirdOrderNonLin.process (distortion.py:91-98, :191-198, :281) on n complex samples */
 int mmimo_pa_process(mmimo_ctx* ctx, const mmimo_pa_desc* pa, size_t n, const float* in, float* out);
 /* modulation.modulate (modulation.py:13-25): bits -> n_sym constellation points */

@@ -61,8 +61,8 @@ EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_er
            "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_sweep", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
            "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
-           "mmimo_fft", "mmimo_welch_psd", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr", "mmimo_array_transmit",
-           "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
+           "mmimo_fft", "mmimo_welch_psd", "mmimo_welch_psd_noalloc", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr",
+           "mmimo_array_transmit", "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
            "mmimo_channel_geometric", "mmimo_channel_fspl", "mmimo_channel_random_paths", "mmimo_precoding",
            "mmimo_agc", "mmimo_cnc_receive", "mmimo_mcnc_receive"]
 
@@ -110,6 +110,9 @@ def load(build_if_missing: bool = True):
     lib.mmimo_sdr_simulate.argtypes = [C.c_void_p, C.POINTER(SdrRequest), c_d_p, c_d_p]
     lib.mmimo_mu_link_simulate.argtypes = [C.c_void_p, C.POINTER(MuRequest), C.POINTER(MuResult)]
     lib.mmimo_mu_link_simulate.restype = C.c_int
+    # device pointers as integers (size_t n, x_dev, nperseg, nfft, fs, psd_dev, stream)
+    lib.mmimo_welch_psd_noalloc.argtypes = [C.c_size_t, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p]
+    lib.mmimo_welch_psd_noalloc.restype = C.c_int
     lib.mmimo_link_sweep.argtypes = [C.c_void_p, C.POINTER(SimRequest), C.c_int32, C.c_int32, c_d_p, c_d_p, c_u64_p]
     lib.mmimo_link_sweep.restype = C.c_int
     lib.mmimo_launch_count.argtypes = [C.c_void_p]

@@ -438,3 +438,72 @@ extern "C" int mmimo_measure_fp32_peak(mmimo_ctx* c, double* tflops) {
 #include "link_host.inl"
 #include "mu_host.inl"
 #include "stage_host.inl"
+
+// ---------------------------------------------------------------------------------------------
+// mmimo_welch_psd_noalloc (include/mmimo_b200.h): the Welch PSD of stage_host.inl for callers that may not allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The three scratch arrays of mmimo_welch_psd (windowed segments, their spectra, the double accumulator) live in ONE
+// file-scope device array of fixed size; every GPU that loads the library holds it until the process exits.
+// All calls share it: calls that overlap on one GPU (different streams, different host threads) race.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t NOALLOC_MAX_ELEMS = MMIMO_WELCH_NOALLOC_MAX_ELEMS;          // n_seg * nfft complex samples per call
+constexpr size_t NOALLOC_ROWS_OFF = 0;
+constexpr size_t NOALLOC_SPEC_OFF = NOALLOC_MAX_ELEMS * 8;
+constexpr size_t NOALLOC_ACC_OFF = 2 * NOALLOC_MAX_ELEMS * 8;
+constexpr size_t NOALLOC_BYTES = NOALLOC_ACC_OFF + 8192 * 8;                 // 8 MiB + 64 KiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+#include <mutex>
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of g_noalloc_scratch, per device (the name itself
+                                                           // is only a host-side handle: never hand it to a kernel)
+
+// once per device, with that device current: the array's device address and the transform's shared-memory opt-in
+static int noalloc_setup(int dev, unsigned char** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        unsigned char* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) return fail("mmimo_welch_psd_noalloc: cudaGetSymbolAddress returned NULL");
+        CK(cudaFuncSetAttribute(k_fft_generic_rows<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 8192 * 8));
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+extern "C" int mmimo_welch_psd_noalloc(size_t n, const float* x_dev, int nperseg, int nfft, double fs, double* psd_dev, void* stream) {
+    if (!x_dev || !psd_dev) return fail("mmimo_welch_psd_noalloc: NULL buffer");
+    if (nfft < 8 || nfft > 8192 || (nfft & (nfft - 1))) return fail("mmimo_welch_psd_noalloc: nfft must be a power of two in 8..8192 (got %d)", nfft);
+    if (nperseg < 2 || nperseg > nfft) return fail("mmimo_welch_psd_noalloc: nperseg must be 2..nfft (got %d)", nperseg);
+    if ((size_t)nperseg > n) return fail("mmimo_welch_psd_noalloc: the signal is shorter than one segment (%zu < %d)", n, nperseg);
+    if (!(fs > 0.0)) return fail("mmimo_welch_psd_noalloc: fs must be positive");
+    const int step = nperseg - nperseg / 2;
+    const size_t n_seg = (n - (size_t)(nperseg / 2)) / (size_t)step;
+    if (n_seg > NOALLOC_MAX_ELEMS / (size_t)nfft)
+        return fail("mmimo_welch_psd_noalloc: %zu segments x nfft %d = %zu samples of scratch, the static array holds %zu "
+                    "(MMIMO_WELCH_NOALLOC_MAX_ELEMS); use mmimo_welch_psd for longer signals",
+                    n_seg, nfft, n_seg * (size_t)nfft, NOALLOC_MAX_ELEMS);
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail("mmimo_welch_psd_noalloc: device ordinal %d out of range", dev);
+    unsigned char* base = nullptr;
+    if (noalloc_setup(dev, &base)) return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    const float2* dx = reinterpret_cast<const float2*>(x_dev);
+    float2* rows = reinterpret_cast<float2*>(base + NOALLOC_ROWS_OFF);
+    float2* spec = reinterpret_cast<float2*>(base + NOALLOC_SPEC_OFF);
+    double* acc = reinterpret_cast<double*>(base + NOALLOC_ACC_OFF);
+    // the array keeps the previous call's contents: the accumulator must start at zero; rows / spec are fully overwritten
+    CK(cudaMemsetAsync(acc, 0, (size_t)nfft * 8, st));
+    k_welch_segments<<<(unsigned)n_seg, 256, 0, st>>>(dx, rows, nperseg, step, nfft);
+    k_fft_generic_rows<-1><<<(unsigned)n_seg, 256, 2 * (size_t)nfft * 8, st>>>(rows, spec, nfft, ilog2(nfft), 0, 0);
+    k_welch_reduce<<<(nfft + 255) / 256, 256, 0, st>>>(spec, acc, (int)n_seg, nfft);
+    double w2 = 0.0;
+    for (int i = 0; i < nperseg; ++i) { const double w = 0.5 - 0.5 * cos(2.0 * M_PI * i / nperseg); w2 += w * w; }
+    k_scale_d<<<(nfft + 255) / 256, 256, 0, st>>>(acc, (double)nfft / (fs * w2 * (double)n_seg), nfft);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(psd_dev, acc, (size_t)nfft * 8, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
