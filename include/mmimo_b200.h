@@ -329,6 +329,10 @@ int mmimo_profile(mmimo_ctx* ctx, int enable);
 int mmimo_profile_read(mmimo_ctx* ctx, double* ms4, uint64_t* n4);
 /* measured FP32 FMA peak of the device in TFLOP/s (dependent-free FFMA chains on every SM) */
 int mmimo_measure_fp32_peak(mmimo_ctx* ctx, double* tflops);
+/* the unfused building-block kernels of Transceiver.transmit + propagate (transceiver.py:98-174, channel.py:84-89), timed one
+ * by one on `rows` device-resident rows of 4096 samples, `reps` launches each: ms_out[5] = ms per launch of
+ * map+precode, IFFT, soft limiter, FFT, propagate (elementwise form).  rows <= 65535 */
+int mmimo_measure_stage_kernels(mmimo_ctx* ctx, int rows, int reps, double* ms_out);
 
 #ifdef __cplusplus
 }

@@ -59,7 +59,7 @@ _LIB = None
 EXPORTS = ["mmimo_device_count", "mmimo_create", "mmimo_destroy", "mmimo_last_error", "mmimo_version", "mmimo_stream", "mmimo_synchronize",
            "mmimo_set_stream", "mmimo_counters_to_device",
            "mmimo_configure", "mmimo_set_ibo", "mmimo_sdr_simulate", "mmimo_mu_link_simulate", "mmimo_link_sweep", "mmimo_link_simulate", "mmimo_link_enqueue", "mmimo_link_fetch",
-           "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak",
+           "mmimo_launch_count", "mmimo_profile", "mmimo_profile_read", "mmimo_measure_fp32_peak", "mmimo_measure_stage_kernels",
            # stage-level operations (see _stage_abi.STAGE_EXPORTS)
            "mmimo_fft", "mmimo_welch_psd", "mmimo_welch_psd_noalloc", "mmimo_pa_process", "mmimo_qam_map", "mmimo_qam_detect", "mmimo_qam_soft_llr",
            "mmimo_array_transmit", "mmimo_ofdm_demodulate", "mmimo_propagate", "mmimo_awgn_add", "mmimo_count_mismatched_bits",
@@ -120,6 +120,7 @@ def load(build_if_missing: bool = True):
     lib.mmimo_profile.argtypes = [C.c_void_p, C.c_int]
     lib.mmimo_profile_read.argtypes = [C.c_void_p, c_d_p, c_u64_p]
     lib.mmimo_measure_fp32_peak.argtypes = [C.c_void_p, c_d_p]
+    lib.mmimo_measure_stage_kernels.argtypes = [C.c_void_p, C.c_int, C.c_int, c_d_p]
     _bind_stage_ops(lib)
     _LIB = lib
     return lib

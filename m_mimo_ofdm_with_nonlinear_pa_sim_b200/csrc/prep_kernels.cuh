@@ -42,8 +42,32 @@ struct ChanArgs {
 };
 
 // one propagation path: amp / f * exp(+j 2 pi d f / c), amp = gain c / (4 pi d) (channel.py:56-66); the phase (thousands
-// of cycles) is range-reduced in double, the amplitude needs fp32 only.  d_over_c and amp are per (frame, antenna).
-__device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float amp, bool skip_att) {
+// of cycles) is range-reduced in double, the amplitude needs fp32 only.  d_over_c and amp are per (frame, antenna), rf is
+// the fp32 reciprocal of the sub-carrier frequency (per slot, loop-invariant in the callers).
+#ifndef CHAN_FAST
+#define CHAN_FAST 1
+#endif
+#if CHAN_FAST
+// x = d f / c in turns.  4x = n + u with n integer and |u| <= 1/2 comes out of three double operations (round-to-integer
+// by the 1.5 * 2^52 constant, the quadrant n mod 4 sits in the low word of the sum, the second FMA returns the EXACT
+// remainder of the product), then cos / sin of (pi/2) u are two degree-3 polynomials in u^2 (max error 1.2e-7) and the
+// quadrant turns them by j^n.  24 instructions per coefficient instead of ~40 through sincospif and a division.
+__device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float rf, float amp, bool skip_att) {
+    const double t4 = 4.0 * d_over_c;
+    const double big = fma(t4, f, 6755399441055744.0);
+    const int q = __double2loint(big);
+    const float u = (float)fma(t4, f, -(big - 6755399441055744.0));
+    const float z = u * u;
+    const float sn = u * fmaf(z, fmaf(z, fmaf(z, -0.004604428540915251f, 0.0796811580657959f), -0.6459636092185974f), 1.5707963705062866f);
+    const float cs = fmaf(z, fmaf(z, fmaf(z, -0.02042119763791561f, 0.2536039352416992f), -1.2336976528167725f), 1.0f);
+    const bool sw = q & 1;
+    const float a = skip_att ? 1.0f : amp * rf;
+    const float re = __int_as_float(__float_as_int(sw ? sn : cs) ^ (((q + 1) & 2) << 30));
+    const float im = __int_as_float(__float_as_int(sw ? cs : sn) ^ ((q & 2) << 30));
+    return make_float2(a * re, a * im);
+}
+#else
+__device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float rf, float amp, bool skip_att) {
     const double x = d_over_c * f;
     const float r = (float)(x - rint(x));
     float s, c;
@@ -51,6 +75,10 @@ __device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float am
     if (skip_att) return make_float2(c, s);
     const float a = amp / (float)f;
     return make_float2(a * c, a * s);
+}
+#endif
+__device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float amp, bool skip_att) {
+    return path_coeff(d_over_c, f, 1.0f / (float)f, amp, skip_att);
 }
 
 // the same from distance and linear gain (stage kernels: one realisation per call)
@@ -108,6 +136,9 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
     double2 fr[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) fr[j] = *reinterpret_cast<const double2*>(a.freq_slot + j * 512 + 2 * t);
+    float2 rf[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) rf[j] = make_float2(1.0f / (float)fr[j].x, 1.0f / (float)fr[j].y);
     const int nk = min(per_cta, a.n_ant - kb);
     float nrm[8];
 #pragma unroll
@@ -119,11 +150,11 @@ __global__ void __launch_bounds__(256) k_gen_channel(const ChanArgs a) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int p = j * 512 + 2 * t;
-            float2 h0 = path_coeff(t1, fr[j].x, amp1, a.skip_attenuation);
-            float2 h1 = path_coeff(t1, fr[j].y, amp1, a.skip_attenuation);
+            float2 h0 = path_coeff(t1, fr[j].x, rf[j].x, amp1, a.skip_attenuation);
+            float2 h1 = path_coeff(t1, fr[j].y, rf[j].y, amp1, a.skip_attenuation);
             if (a.kind == 1) {
-                const float2 g0 = path_coeff(t2, fr[j].x, amp2, a.skip_attenuation);
-                const float2 g1 = path_coeff(t2, fr[j].y, amp2, a.skip_attenuation);
+                const float2 g0 = path_coeff(t2, fr[j].x, rf[j].x, amp2, a.skip_attenuation);
+                const float2 g1 = path_coeff(t2, fr[j].y, rf[j].y, amp2, a.skip_attenuation);
                 h0.x -= g0.x; h0.y -= g0.y;
                 h1.x -= g1.x; h1.y -= g1.y;
             }

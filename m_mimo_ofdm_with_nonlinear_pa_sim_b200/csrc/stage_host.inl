@@ -604,3 +604,56 @@ extern "C" int mmimo_mcnc_receive(mmimo_ctx* c, const mmimo_modem_desc* m, const
     CK(cudaStreamSynchronize(c->stream));
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// mmimo_measure_stage_kernels (bench.py, "stages"): the unfused building-block kernels of one array transmit + propagate
+// (k_map_precode -> k_fft4096_rows<+1> -> k_pa<soft limiter> -> k_fft4096_rows<-1> -> k_propagate) timed one by one with
+// CUDA events on the context stream over `rows` device-resident rows of 4096 samples (rows * 32 KiB per buffer: larger than
+// L2 for rows >= 8192), `reps` timed launches each after one warm-up.  ms_out[5] = average ms per launch in that order.
+// These are HBM-bound kernels; a single stage call of the drop-in classes (64 rows, host buffers) is latency-bound instead.
+// ---------------------------------------------------------------------------------------------
+extern "C" int mmimo_measure_stage_kernels(mmimo_ctx* c, int rows, int reps, double* ms_out) {
+    STAGE_PROLOGUE(c);
+    if (!ms_out || rows < 1 || rows > 65535 || reps < 1) return fail("mmimo_measure_stage_kernels: rows 1..65535, reps >= 1");
+    const int n = 4096, ns = 2048;
+    const size_t nfd = (size_t)rows * n, nv = (size_t)rows * ns;
+    if (ar.begin(4 * Arena::pad(nfd * 8) + 2 * Arena::pad(nv * 8) + Arena::pad(ns))) return 1;
+    float2* grid = ar.get<float2>(nfd);
+    float2* td = ar.get<float2>(nfd);
+    float2* td_pa = ar.get<float2>(nfd);
+    float2* fd = ar.get<float2>(nfd);
+    float2* v = ar.get<float2>(nv);
+    uint8_t* idx = ar.get<uint8_t>(ns);
+    CK(cudaMemsetAsync(v, 0x3c, nv * 8, c->stream));  // 0x3c3c3c3c = 0.0115f
+    CK(cudaMemsetAsync(idx, 0x15, ns, c->stream));
+    MapArgs ma{};
+    ma.idx = idx; ma.v = v; ma.extra = nullptr; ma.grid = grid;
+    ma.n_users = 1; ma.n_ant = rows; ma.n_fft = n; ma.n_sc = ns; ma.per_user = 0;
+    ma.q.log2side = 3; ma.scale = 1.f; ma.w_self = 1.f; ma.w_extra = 0.f;
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    int rc = 0;
+    for (int kern = 0; kern < 5 && !rc; ++kern) {
+        for (int rep = -1; rep < reps; ++rep) {  // rep -1: warm-up, then `reps` launches inside one event pair
+            if (rep == 0) cudaEventRecord(a, c->stream);
+            switch (kern) {
+                case 0: k_map_precode<<<dim3(nblk(n), rows, 1), 256, 0, c->stream>>>(ma); break;
+                case 1: rc = fft_dev(c, true, n, rows, 0, 0, grid, td); break;
+                case 2: k_pa<PA_SOFT_LIMITER><<<nblk(nfd), 256, 0, c->stream>>>(td, td_pa, nfd, 1e-4f, 0.f); break;
+                case 3: rc = fft_dev(c, false, n, rows, 0, 0, td_pa, fd); break;
+                case 4: k_propagate<<<dim3(nblk(n), rows), 256, 0, c->stream>>>(fd, grid, td, rows, n, 0); break;
+            }
+            if (kern != 1 && kern != 3) c->launches++;
+            if (rc) break;
+        }
+        cudaEventRecord(b, c->stream);
+        if (cudaEventSynchronize(b) != cudaSuccess || cudaGetLastError() != cudaSuccess) { rc = fail("mmimo_measure_stage_kernels: kernel %d failed", kern); break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        ms_out[kern] = (double)ms / reps;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    return rc;
+}

@@ -325,6 +325,17 @@ class LinkEngine:
         _lib.check(self._lib, self._lib.mmimo_measure_fp32_peak(self._h, C.byref(v)))
         return float(v.value)
 
+    STAGE_KERNELS = ("map_precode", "ifft", "pa_soft_limiter", "fft", "propagate")
+    # algorithmic HBM bytes per row of 4096 complex64 samples: map reads the 16 KiB precoder row and writes the grid row;
+    # the transforms and the PA read and write one row; propagate reads two rows and writes one
+    STAGE_BYTES_PER_ROW = (16384 + 32768, 65536, 65536, 65536, 98304)
+
+    def measure_stage_kernels(self, rows: int = 16384, reps: int = 5):
+        """ms per launch of the five unfused building-block kernels on `rows` device-resident rows (mmimo_measure_stage_kernels)."""
+        ms = np.zeros(5, np.float64)
+        _lib.check(self._lib, self._lib.mmimo_measure_stage_kernels(self._h, int(rows), int(reps), _ptr(ms, C.c_double)))
+        return dict(zip(self.STAGE_KERNELS, ms.tolist()))
+
     @property
     def stream_ptr(self) -> int:
         return int(self._lib.mmimo_stream(self._h) or 0)
