@@ -237,11 +237,24 @@ def secondary_workloads(eng, a, snr, peak):
         run("mu_" + tag, lambda tag=tag: eng.mu_simulate(F // 2, I, snr, precoding=tag, seed=11), 2 * (F // 2),
             2.0 * K * (I + 1) * fft)
     run("sdr", lambda: eng.sdr(F, seed=3), F, 2.0 * K * fft)
-    for v in out.values():
+    for v in list(out.values()):
         v["note"] = "device RNG, K=%d, I=%d, soft limiter IBO 0 dB" % (K, I)
     out["mu_mrt"]["unit"] = out["mu_zf"]["unit"] = "user-frames/s"
     out["sdr"]["unit"] = "snapshots/s"
     eng.configure(n_ant=K, channel="los", receiver="mcnc", pa="softlim", ibo_db=0.0)
+    # the unfused building-block kernels (Transceiver.transmit + propagate stage by stage): HBM-bound, measured on 16384
+    # device-resident rows (512 MiB per array, larger than L2) against the measured copy bandwidth
+    hbm = float(measured_peaks().get("hbm_gbs", 6543.4))
+    rows = 16384
+    ms = eng.measure_stage_kernels(rows, 5)
+    out["stages"] = {"bound": "hbm", "rows": rows, "row_samples": N_FFT, "peak_gbs": hbm,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)" if "hbm_gbs" in measured_peaks() else "fallback 6543.4",
+                     "kernels": {k: {"ms_per_launch": ms[k], "algorithmic_bytes": b * rows,
+                                     "achieved_gbs": b * rows / (ms[k] * 1e-3) * 1e-9, "frac": b * rows / (ms[k] * 1e-3) * 1e-9 / hbm}
+                                 for k, b in zip(eng.STAGE_KERNELS, eng.STAGE_BYTES_PER_ROW)},
+                     "note": "k_map_precode, k_fft4096_rows<+1>, k_pa<soft limiter>, k_fft4096_rows<-1>, k_propagate timed one by one "
+                             "with CUDA events (mmimo_measure_stage_kernels); one stage call of the drop-in classes (64 rows, host "
+                             "buffers) is latency-bound, this is the kernels' own rate"}
     return out
 
 

@@ -41,6 +41,11 @@ namespace mmimo {
 #ifndef T64_EPI_EARLY
 #define T64_EPI_EARLY 1  // the AGC row of the pass epilogue is loaded before the antenna groups meet (L2 latency under the barriers)
 #endif
+#ifndef T64_FIRST_ROW
+#define T64_FIRST_ROW 0  // where the copy of a group's FIRST precoder row of a pass starts: 0 after the symbols of the pass are
+                         // written (round-2 form); 1 at the very top of the pass (under the symbol prologue); 2 in the group's
+                         // last chain of the PREVIOUS pass (under the pass epilogue), else at the top of the pass
+#endif
 #ifndef T64_PA_UNIT
 #define T64_PA_UNIT 1  // PA evaluated on the signal scaled to a unit threshold (one multiply less per sample)
 #endif
@@ -160,6 +165,20 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
             // PA compares against 1 and needs no per-sample multiply by sqrt(P); the factor returns after the antenna sum
             const float pa_out_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? 1.0f / sqrt_p0 : sqrt_p0;
             const float pa_in_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? sqrt_p0 : 1.0f / sqrt_p0;
+            if (T64_FIRST_ROW && g < K && lane == 0) {
+                // T64_FIRST_ROW 2: was the row already requested by this group's last chain of the previous pass?  (it was if
+                // that pass existed in this CTA and gave the group a chain; all quantities are uniform kernel arguments)
+                bool ahead = false;
+                if (T64_FIRST_ROW == 2 && !(first && f == (int)blockIdx.x)) {
+                    const int kprev = pass >= 2 || (first && a.n_iter > 0) ? a.loop.k : (a.rx_eq_in ? 0 : a.tx.k);
+                    ahead = g < kprev;
+                }
+                if (!ahead) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_expect_tx(mbB, ROW_BYTES);
+                    bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
+                }
+            }
             {
                 const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs;
 #pragma unroll
@@ -177,9 +196,11 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
 
             if (g < K) {  // precoder row of the group's first antenna
                 if (lane == 0) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    mbar_expect_tx(mbB, ROW_BYTES);
-                    bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
+                    if (!T64_FIRST_ROW) {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_expect_tx(mbB, ROW_BYTES);
+                        bulk_g2s(smem_u32(rowB), Hp + (size_t)g * N_SC, ROW_BYTES, mbB);
+                    }
                     bulk_prefetch_l2(Hm + (size_t)g * N_SC, ROW_BYTES);
                     if (g + R64_GROUPS < K) bulk_prefetch_l2(Hp + (size_t)(g + R64_GROUPS) * N_SC, ROW_BYTES);
                     if (MU && two_usr) {
@@ -253,6 +274,15 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_link_frame_t64(const FrameAr
                             if (k + 2 * R64_GROUPS < K) {
                                 bulk_prefetch_l2(Hp + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
                                 if (MU && two_usr) bulk_prefetch_l2(Ho + (size_t)(k + 2 * R64_GROUPS) * N_SC, ROW_BYTES);
+                            }
+                        } else if (T64_FIRST_ROW == 2) {  // the group's last chain of this pass: first row of its next pass
+                            const bool last = pass == a.n_iter;
+                            const int nf = last ? f + (int)gridDim.x : f;
+                            const TxSide& nsd = last ? a.tx : a.loop;
+                            if (nf < a.n_frames && !(last && a.rx_eq_in) && g < nsd.k) {
+                                const float2* __restrict__ Hn = nsd.v ? nsd.v + nf * nsd.v_fs : nsd.h_pre + nf * nsd.h_pre_fs;
+                                mbar_expect_tx(mbB, ROW_BYTES);
+                                bulk_g2s(smem_u32(rowB), Hn + (size_t)g * N_SC, ROW_BYTES, mbB);
                             }
                         }
                     }

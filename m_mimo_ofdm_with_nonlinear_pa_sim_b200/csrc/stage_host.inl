@@ -2,8 +2,8 @@
 // Every entry point: H2D of the caller's arrays -> stage kernels on the context stream -> D2H -> synchronize.
 
 static int stage_kernels_init() {
-    cudaError_t e = cudaFuncSetAttribute(k_fft4096_rows<+1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 256) * 8);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fft4096_rows<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (8192 + 256) * 8);
+    cudaError_t e = cudaFuncSetAttribute(k_fft4096_rows<+1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_ROWS_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fft4096_rows<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_ROWS_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fft_generic_rows<+1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 8192 * 8);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fft_generic_rows<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 8192 * 8);
     if (e != cudaSuccess) return fail("stage_kernels_init: %s", cudaGetErrorString(e));
@@ -41,8 +41,8 @@ static int ilog2(int n) { int l = 0; while ((1 << l) < n) ++l; return l; }
 static int fft_dev(mmimo_ctx* c, bool inverse, int n, int rows, int skip, int cp, const float2* in, float2* out) {
     if (rows <= 0) return 0;
     if (n == 4096) {
-        if (inverse) k_fft4096_rows<+1><<<rows, FFT_THREADS, (8192 + 256) * 8, c->stream>>>(in, out, c->tw4096.as<float2>(), c->tw256.as<float2>(), skip, cp);
-        else k_fft4096_rows<-1><<<rows, FFT_THREADS, (8192 + 256) * 8, c->stream>>>(in, out, c->tw4096.as<float2>(), c->tw256.as<float2>(), skip, cp);
+        if (inverse) k_fft4096_rows<+1><<<rows, FFT_THREADS, FFT_ROWS_SMEM, c->stream>>>(in, out, c->tw4096.as<float2>(), c->tw256.as<float2>(), skip, cp);
+        else k_fft4096_rows<-1><<<rows, FFT_THREADS, FFT_ROWS_SMEM, c->stream>>>(in, out, c->tw4096.as<float2>(), c->tw256.as<float2>(), skip, cp);
     } else {
         if (inverse) k_fft_generic_rows<+1><<<rows, 256, 2 * n * 8, c->stream>>>(in, out, n, ilog2(n), skip, cp);
         else k_fft_generic_rows<-1><<<rows, 256, 2 * n * 8, c->stream>>>(in, out, n, ilog2(n), skip, cp);
@@ -52,13 +52,20 @@ static int fft_dev(mmimo_ctx* c, bool inverse, int n, int rows, int skip, int cp
     return 0;
 }
 
+template <int KIND>
+static void pa_launch(mmimo_ctx* c, size_t n, const float2* in, float2* out, float p0, float p1) {
+    if (n % 2 == 0 && (((uintptr_t)in | (uintptr_t)out) & 15) == 0)
+        k_pa4<KIND><<<nblk(n / 2, 512), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out), n / 2, p0, p1);
+    else
+        k_pa<KIND><<<nblk(n), 256, 0, c->stream>>>(in, out, n, p0, p1);
+}
 static int pa_dev(mmimo_ctx* c, const mmimo_pa_desc* pa, size_t n, const float2* in, float2* out) {
     const float p0 = (float)pa->p0, p1 = (float)pa->p1;
     switch (pa->kind) {
         case MMIMO_PA_NONE: CK(cudaMemcpyAsync(out, in, n * 8, cudaMemcpyDeviceToDevice, c->stream)); return 0;
-        case MMIMO_PA_SOFT_LIMITER: k_pa<PA_SOFT_LIMITER><<<nblk(n), 256, 0, c->stream>>>(in, out, n, p0, p1); break;
-        case MMIMO_PA_RAPP: k_pa<PA_RAPP><<<nblk(n), 256, 0, c->stream>>>(in, out, n, p0, p1); break;
-        case MMIMO_PA_TOI: k_pa<PA_TOI><<<nblk(n), 256, 0, c->stream>>>(in, out, n, p0, p1); break;
+        case MMIMO_PA_SOFT_LIMITER: pa_launch<PA_SOFT_LIMITER>(c, n, in, out, p0, p1); break;
+        case MMIMO_PA_RAPP: pa_launch<PA_RAPP>(c, n, in, out, p0, p1); break;
+        case MMIMO_PA_TOI: pa_launch<PA_TOI>(c, n, in, out, p0, p1); break;
         default: return fail("unknown pa kind %d", pa->kind);
     }
     c->launches++;
@@ -80,7 +87,7 @@ static int array_transmit_dev(mmimo_ctx* c, const mmimo_modem_desc* m, Qam q, co
     ma.idx = t.idx; ma.v = t.v; ma.extra = t.extra; ma.grid = grid;
     ma.n_users = t.n_users; ma.n_ant = t.n_ant; ma.n_fft = m->n_fft; ma.n_sc = m->n_sub_carr; ma.per_user = t.per_user;
     ma.q = q; ma.scale = (float)m->constel_scale; ma.w_self = t.w_self; ma.w_extra = t.w_extra;
-    k_map_precode<<<dim3(nblk(m->n_fft), t.n_ant, G), 256, 0, c->stream>>>(ma);
+    k_map_precode<<<dim3(nblk(m->n_fft / 4), t.n_ant, G), 256, 0, c->stream>>>(ma);
     c->launches++;
     const size_t nfd = (size_t)rows * m->n_fft;
     if (skip) {
@@ -638,9 +645,9 @@ extern "C" int mmimo_measure_stage_kernels(mmimo_ctx* c, int rows, int reps, dou
         for (int rep = -1; rep < reps; ++rep) {  // rep -1: warm-up, then `reps` launches inside one event pair
             if (rep == 0) cudaEventRecord(a, c->stream);
             switch (kern) {
-                case 0: k_map_precode<<<dim3(nblk(n), rows, 1), 256, 0, c->stream>>>(ma); break;
+                case 0: k_map_precode<<<dim3(nblk(n / 4), rows, 1), 256, 0, c->stream>>>(ma); break;
                 case 1: rc = fft_dev(c, true, n, rows, 0, 0, grid, td); break;
-                case 2: k_pa<PA_SOFT_LIMITER><<<nblk(nfd), 256, 0, c->stream>>>(td, td_pa, nfd, 1e-4f, 0.f); break;
+                case 2: pa_launch<PA_SOFT_LIMITER>(c, nfd, td, td_pa, 1e-4f, 0.f); break;
                 case 3: rc = fft_dev(c, false, n, rows, 0, 0, td_pa, fd); break;
                 case 4: k_propagate<<<dim3(nblk(n), rows), 256, 0, c->stream>>>(fd, grid, td, rows, n, 0); break;
             }

@@ -96,15 +96,12 @@ __global__ void k_soft_llr(const float2* __restrict__ in, const double* __restri
 //   grid  [G][K][n_fft]      G = U when per_user (sum_usr_signals=False), else 1
 // ---------------------------------------------------------------------------------------------
 struct MapArgs {
-    const uint8_t* idx; const float2* v; const float2* extra; float2* grid;
+    const uint8_t* __restrict__ idx; const float2* __restrict__ v; const float2* __restrict__ extra; float2* __restrict__ grid;
     int n_users, n_ant, n_fft, n_sc, per_user;
     Qam q; float scale;       // constellation scale
     float w_self, w_extra;    // weights of the mapped symbols and of `extra`
 };
-__global__ void k_map_precode(const MapArgs a) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= a.n_fft) return;
-    const int k = blockIdx.y, g = blockIdx.z;
+__device__ __forceinline__ float2 map_precode_bin(const MapArgs& a, int n, int k, int g) {
     const int s = sc_of_bin(n, a.n_fft, a.n_sc);
     float2 acc = make_float2(0.f, 0.f);
     if (s >= 0) {
@@ -120,7 +117,19 @@ __global__ void k_map_precode(const MapArgs a) {
             acc.x = fmaf(a.w_extra, e.x, acc.x); acc.y = fmaf(a.w_extra, e.y, acc.y);
         }
     }
-    a.grid[((size_t)g * a.n_ant + k) * a.n_fft + n] = acc;
+    return acc;
+}
+// four bins per thread (n, n + n_fft/4, ...): contiguous 8-byte accesses per warp, four independent loads in flight
+__global__ void __launch_bounds__(256) k_map_precode(const MapArgs a) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x, q = a.n_fft >> 2;
+    if (n >= q) return;
+    const int k = blockIdx.y, g = blockIdx.z;
+    float2 y[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) y[j] = map_precode_bin(a, n + j * q, k, g);
+    float2* row = a.grid + ((size_t)g * a.n_ant + k) * a.n_fft + n;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) row[j * q] = y[j];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -131,14 +140,23 @@ __global__ void k_map_precode(const MapArgs a) {
 // `skip` input samples are dropped in front of each input row (cyclic prefix removal, utilities.py:323);
 // `cp` samples are prepended to each output row (modulation.py:273).
 // ---------------------------------------------------------------------------------------------
+#ifndef FFT_ROWS_ONEBUF
+#define FFT_ROWS_ONEBUF 1
+#endif
+// one exchange buffer for both exchanges of a transform (a barrier in front of each store phase): 35 KB instead of 67 KB
+// of shared memory per CTA, so that four CTAs instead of three are resident per SM (the kernel is HBM-latency-bound)
+struct SyncCtaOneBuf : SyncCta {
+    __device__ __forceinline__ void x_begin() const { __syncthreads(); }
+};
+constexpr int FFT_ROWS_SMEM = ((FFT_ROWS_ONEBUF ? 4096 : 8192) + 256) * 8;
 template <int S>
-__global__ void __launch_bounds__(FFT_THREADS) k_fft4096_rows(const float2* __restrict__ in, float2* __restrict__ out,
+__global__ void __launch_bounds__(FFT_THREADS, FFT_ROWS_ONEBUF ? 4 : 3) k_fft4096_rows(const float2* __restrict__ in, float2* __restrict__ out,
                                                               const float2* __restrict__ tw4096, const float2* __restrict__ tw256,
                                                               int skip, int cp) {
     extern __shared__ float2 smem[];
     pf2* bufA = reinterpret_cast<pf2*>(smem);
-    pf2* bufB = reinterpret_cast<pf2*>(smem + 4096);
-    float2* tw2 = smem + 8192;
+    pf2* bufB = FFT_ROWS_ONEBUF ? bufA : reinterpret_cast<pf2*>(smem + 4096);
+    float2* tw2 = smem + (FFT_ROWS_ONEBUF ? 4096 : 8192);
     const int t = threadIdx.x;
     tw2[t] = tw256[t];
     Tw1 tw1;
@@ -149,7 +167,11 @@ __global__ void __launch_bounds__(FFT_THREADS) k_fft4096_rows(const float2* __re
     pf2 x[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) x[j] = pk2(src[t + 256 * j]);
+#if FFT_ROWS_ONEBUF
+    fft4096<S, false, false, SyncCtaOneBuf>(x, bufA, bufB, tw2, tw1, t);
+#else
     fft4096<S, false, false>(x, bufA, bufB, tw2, tw1, t);
+#endif
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
         const float2 y = unpk(x[j]);
@@ -210,6 +232,23 @@ __global__ void k_pa(const float2* __restrict__ in, float2* __restrict__ out, si
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     out[i] = pa_apply<KIND>(in[i], p0, sqrtf(p0), p1);
+}
+// the same on four samples per thread (two 16-byte loads in flight, 16-byte stores): n even, both pointers 16-byte aligned
+template <int KIND>
+__global__ void __launch_bounds__(256) k_pa4(const float4* __restrict__ in, float4* __restrict__ out, size_t n_pairs, float p0, float p1) {
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    const float sp = sqrtf(p0);
+    if (i + 1 < n_pairs) {
+        const float4 a = in[i], b = in[i + 1];
+        const float2 a0 = pa_apply<KIND>(make_float2(a.x, a.y), p0, sp, p1), a1 = pa_apply<KIND>(make_float2(a.z, a.w), p0, sp, p1);
+        const float2 b0 = pa_apply<KIND>(make_float2(b.x, b.y), p0, sp, p1), b1 = pa_apply<KIND>(make_float2(b.z, b.w), p0, sp, p1);
+        out[i] = make_float4(a0.x, a0.y, a1.x, a1.y);
+        out[i + 1] = make_float4(b0.x, b0.y, b1.x, b1.y);
+    } else if (i < n_pairs) {
+        const float4 a = in[i];
+        const float2 a0 = pa_apply<KIND>(make_float2(a.x, a.y), p0, sp, p1), a1 = pa_apply<KIND>(make_float2(a.z, a.w), p0, sp, p1);
+        out[i] = make_float4(a0.x, a0.y, a1.x, a1.y);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
