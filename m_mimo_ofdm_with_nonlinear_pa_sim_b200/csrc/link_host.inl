@@ -364,15 +364,39 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         if (c->rxeq_scr.reserve((size_t)8 * c->n_sm * N_SC * 8)) return 1;  // >= the largest grid launch_frame uses
         fa.rxeq_scratch = c->rxeq_scr.as<float2>();
         const int grid = n;
+        // CncReceiver: the frame kernel runs the real transmission only (pass 0 -> equalised received signal), the receiver
+        // loop runs one frame per 64-thread group in k_cnc_loop_t64 (cnc_loop_t64.cuh); identical decisions and counters
+        const bool cnc_split = !mcnc && c->cnc_split && c->frame_kernel == 0 && I > 0;
+        FrameArgs f2 = fa;
+        if (cnc_split) {
+            fa.n_iter = 0;
+            fa.det_out = nullptr; fa.corr_out = nullptr; fa.err_out = nullptr; fa.err_total = nullptr;
+            fa.rx_eq_out = c->rx_eq.as<float2>();
+            f2.rx_eq_in = c->rx_eq.as<float2>();
+            if (f2.err_out) CK(cudaMemsetAsync(c->err.p, 0, (size_t)n * (I + 1) * 4, c->stream));
+        }
+        const int grid2 = std::min((n + R64_GROUPS - 1) / R64_GROUPS, c->n_sm);
         prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {
-            case MMIMO_PA_NONE: launch_frame<PA_NONE>(fa, c, grid); break;
-            case MMIMO_PA_SOFT_LIMITER: launch_frame<PA_SOFT_LIMITER>(fa, c, grid); break;
-            case MMIMO_PA_RAPP: launch_frame<PA_RAPP>(fa, c, grid); break;
-            default: launch_frame<PA_TOI>(fa, c, grid); break;
+            case MMIMO_PA_NONE:
+                launch_frame<PA_NONE>(fa, c, grid);
+                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                break;
+            case MMIMO_PA_SOFT_LIMITER:
+                launch_frame<PA_SOFT_LIMITER>(fa, c, grid);
+                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                break;
+            case MMIMO_PA_RAPP:
+                launch_frame<PA_RAPP>(fa, c, grid);
+                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                break;
+            default:
+                launch_frame<PA_TOI>(fa, c, grid);
+                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                break;
         }
         prof_end(c);
-        c->launches++;
+        c->launches += cnc_split ? 2 : 1;
         CK(cudaGetLastError());
         if (pipelined) {
             CK(cudaEventRecord(c->cur_released, c->stream));

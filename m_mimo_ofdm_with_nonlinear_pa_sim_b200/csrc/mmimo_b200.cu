@@ -16,6 +16,7 @@
 #include "mu_kernels.cuh"
 #include "frame_kernel_r64.cuh"
 #include "frame_kernel_t64.cuh"
+#include "cnc_loop_t64.cuh"
 #include "stage_kernels.cuh"
 
 using namespace mmimo;
@@ -72,6 +73,7 @@ struct mmimo_ctx {
     int frame_kernel = 0;
     // start offset (SM cycles) of antenna groups 2,3 of k_link_frame_t64 (FrameArgs::stagger); MMIMO_T64_STAGGER overrides
     int t64_stagger = 0;
+    int cnc_split = CNC_SPLIT;  // CNC frames: pass 0 in the frame kernel, the receiver loop in k_cnc_loop_t64 (MMIMO_CNC_SPLIT=0/1)
     // closed-form realisation kernel for LOS + MRT (k_prep_los); MMIMO_PREP_ANALYTIC=0 keeps k_prep_realisation (A/B knob)
     int prep_analytic = 1;
     int ctas_per_sm_r16 = 2;
@@ -200,6 +202,7 @@ extern "C" int mmimo_create(mmimo_ctx** out, int device) {
     if (const char* e = getenv("MMIMO_PREP_ANALYTIC")) c->prep_analytic = atoi(e) != 0;
     if (const char* e = getenv("MMIMO_PIPELINE_PREP")) c->pipeline_prep = atoi(e) != 0;
     if (const char* e = getenv("MMIMO_T64_STAGGER")) c->t64_stagger = std::max(0, atoi(e));
+    if (const char* e = getenv("MMIMO_CNC_SPLIT")) c->cnc_split = atoi(e) != 0;
     if (const char* e = getenv("MMIMO_CTAS_PER_SM")) c->ctas_per_sm_r16 = std::min(8, std::max(1, atoi(e)));
     const int rc = create_body(c);
     if (rc) { mmimo_destroy(c); return rc; }
@@ -255,6 +258,10 @@ static int create_body(mmimo_ctx* c) {
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_cnc_loop_t64<PA_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, CNC_LOOP_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_cnc_loop_t64<PA_SOFT_LIMITER>, cudaFuncAttributeMaxDynamicSharedMemorySize, CNC_LOOP_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_cnc_loop_t64<PA_RAPP>, cudaFuncAttributeMaxDynamicSharedMemorySize, CNC_LOOP_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_cnc_loop_t64<PA_TOI>, cudaFuncAttributeMaxDynamicSharedMemorySize, CNC_LOOP_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_NONE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_SOFT_LIMITER, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));
     CK(cudaFuncSetAttribute(k_link_frame_t64<PA_RAPP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FRAME_T64_SMEM_BYTES_MU));

@@ -245,6 +245,40 @@ def test_radix64_and_radix16_frame_kernels_agree(monkeypatch):
             eng.close()
 
 
+def test_cnc_loop_kernel_matches_single_kernel_form(monkeypatch):
+    """CncReceiver frames: pass 0 in the frame kernel + the receiver loop in k_cnc_loop_t64 (one frame per 64-thread group,
+    the default) against the whole frame in k_link_frame_t64 (MMIMO_CNC_SPLIT=0).  The loop kernel repeats the frame kernel's
+    arithmetic operation by operation, so decisions, corrected symbols, per-frame errors and counters are IDENTICAL; frame
+    counts that leave groups of the last CTA round without a frame (1, 2, 3 mod 4) and injected symbols are covered."""
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    engines = {}
+    try:
+        for split in ("1", "0"):
+            monkeypatch.setenv("MMIMO_CNC_SPLIT", split)
+            engines[split] = LinkEngine(0)
+        monkeypatch.delenv("MMIMO_CNC_SPLIT", raising=False)
+        rng = np.random.default_rng(5)
+        for pa, n_ant, n_frames, n_iter, constel in (("softlim", 8, 13, 3, 64), ("rapp", 4, 602, 2, 16), ("toi", 2, 7, 5, 64),
+                                                     ("softlim", 1, 4, 1, 4), ("none", 3, 9, 2, 256), ("softlim", 64, 150, 5, 64)):
+            inject = None
+            if n_frames == 13:
+                inject = {"tx_idx": rng.integers(0, constel, (n_frames, 2048), dtype=np.uint8)}
+            outs = {}
+            for split, eng in engines.items():
+                eng.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=0.5, receiver="cnc", constel_size=constel)
+                kw = dict(seed=41, dumps=("rx_eq", "det", "corr", "err_per_frame"))
+                if inject:
+                    kw["inject"] = inject
+                outs[split] = eng.simulate(n_frames, n_iter, 16.0, **kw)
+            a, b = outs["1"], outs["0"]
+            for key in ("err", "det", "err_per_frame", "rx_eq", "corr"):
+                assert np.array_equal(a[key], b[key]), (pa, n_ant, n_frames, key)
+            assert (a["err"][0] > 0 or constel == 4) and int(a["err_per_frame"].sum()) == int(a["err"].sum())
+    finally:
+        for eng in engines.values():
+            eng.close()
+
+
 def test_fused_norm_pass_is_bit_identical(engine):
     """From 2 realisations per SM on, k_gen_channel writes the MRT symbol scale itself (one CTA per realisation) and
     k_prep_realisation skips its norm pass; below that the realisation kernel computes it.  Same operation order, so a
