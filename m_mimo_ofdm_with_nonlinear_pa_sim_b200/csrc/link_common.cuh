@@ -121,13 +121,35 @@ __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1,
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-// two U(0,1] 32-bit uniforms -> one CN(0,1)-shaped pair (each component N(0,1)), Box-Muller
+// cos / sin of (pi/2)(n + u), |u| <= 1/2: two degree-3 polynomials in u^2 (max error 1.3e-7), the quadrant n by sign flips
+__device__ __forceinline__ float2 cis_quadrant(const int n, const float u) {
+    const float z = u * u;
+    const float sn = u * fmaf(z, fmaf(z, fmaf(z, -0.004604428540915251f, 0.0796811580657959f), -0.6459636092185974f), 1.5707963705062866f);
+    const float cs = fmaf(z, fmaf(z, fmaf(z, -0.02042119763791561f, 0.2536039352416992f), -1.2336976528167725f), 1.0f);
+    const bool sw = n & 1;
+    return make_float2(__int_as_float(__float_as_int(sw ? sn : cs) ^ (((n + 1) & 2) << 30)),
+                       __int_as_float(__float_as_int(sw ? cs : sn) ^ ((n & 2) << 30)));
+}
+
+// two 32-bit uniforms -> one CN(0,1)-shaped pair (each component N(0,1)), Box-Muller (the frame kernels' noise)
 __device__ __forceinline__ float2 box_muller(uint32_t u0, uint32_t u1) {
     const float a = ((float)u0 + 1.0f) * 2.3283064365386963e-10f;  // (0,1]
     const float r = sqrtf(-2.0f * logf(a));
     float s, c;
     sincospif((float)u1 * (2.0f * 2.3283064365386963e-10f), &s, &c);
     return make_float2(r * c, r * s);
+}
+// the same for the kernels that draw K x 2048 normals per realisation (Rayleigh coefficients, CSI error): radius from
+// MUFU.LG2 / MUFU.SQRT, angle 2 pi u1 / 2^32 reduced in integer arithmetic (nearest quadrant + remainder in [-1/2, 1/2)),
+// ~25 instructions.  (In the frame kernel the draw is 1/3000 of a frame and the precise form keeps its register allocation.)
+__device__ __forceinline__ float2 box_muller_fast(uint32_t u0, uint32_t u1) {
+    const float a = ((float)u0 + 1.0f) * 2.3283064365386963e-10f;  // (0,1]
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(-1.3862943611198906f * __log2f(a)));  // sqrt(-2 ln a)
+    const uint32_t w = u1 + 0x20000000u;  // + 1/8 turn: w >> 30 is the NEAREST quadrant (mod 4)
+    const float u = (float)((int)(w & 0x3fffffffu) - 0x20000000) * 9.313225746154785e-10f;  // [-1/2, 1/2)
+    const float2 cs = cis_quadrant((int)(w >> 30), u);
+    return make_float2(r * cs.x, r * cs.y);
 }
 
 // RNG stream ids (counter word c2)

@@ -105,8 +105,10 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         ra.skip_attenuation = cfg.skip_attenuation;
         ra.seed = rq->seed; ra.frame_id0 = rq->frame_id0 + c0; ra.stream = in.ray_stream;
         ra.h_out = h_true; ra.n_ant = K;
+        sscale_ready = !in.h_loop && !(rq->csi_eps > 0.0) && n >= 2 * c->n_sm;  // as above: fused norm pass
+        ra.sscale_out = sscale_ready ? c->sscale.as<float>() : nullptr;
         prof_begin(c, PROF_CHAN);
-        k_gen_rayleigh<<<dim3(K, n), 256, 0, c->stream>>>(ra);
+        k_gen_rayleigh<<<dim3(sscale_ready ? 1 : (K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, n), 256, 0, c->stream>>>(ra);
         prof_end(c);
         c->launches++;
     } else {
@@ -127,7 +129,12 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         }
         xa.h_in = h_true; xa.h_out = h_loop; xa.eps = (float)rq->csi_eps; xa.scale = (float)sqrt(1.0 - rq->csi_eps * rq->csi_eps);
         xa.seed = rq->seed; xa.frame_id0 = rq->frame_id0 + c0; xa.stream = in.csi_stream; xa.n_ant = K;
-        k_csi_error<<<dim3(K, n), 256, 0, c->stream>>>(xa);
+        // the precoder is derived from the perturbed rows: with one CTA per realisation the kernel also writes their symbol scale
+        sscale_ready = n >= 2 * c->n_sm;
+        xa.sscale_out = sscale_ready ? c->sscale.as<float>() : nullptr;
+        prof_begin(c, PROF_CHAN);
+        k_csi_error<<<dim3(sscale_ready ? 1 : K, n), 256, 0, c->stream>>>(xa);
+        prof_end(c);
         c->launches++;
     }
     // line of sight + MRT from the true channel: closed form in the K path amplitudes, no pass over the channel rows

@@ -83,7 +83,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             ra.skip_attenuation = cfg.skip_attenuation;
             ra.seed = rq->seed; ra.frame_id0 = 2 * rq->frame_id0 + i0; ra.stream = RNG_RAYLEIGH;
             ra.h_out = h; ra.n_ant = K;
-            k_gen_rayleigh<<<dim3(K, ni), 256, 0, c->stream>>>(ra);
+            k_gen_rayleigh<<<dim3((K + CHAN_ANT_PER_CTA - 1) / CHAN_ANT_PER_CTA, ni), 256, 0, c->stream>>>(ra);
             c->launches++;
         } else {
             return fail("mmimo_mu_link_simulate: channel_kind INJECTED needs h in the request");

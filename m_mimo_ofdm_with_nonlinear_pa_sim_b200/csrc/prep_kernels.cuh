@@ -57,13 +57,9 @@ __device__ __forceinline__ float2 path_coeff(double d_over_c, double f, float rf
     const double big = fma(t4, f, 6755399441055744.0);
     const int q = __double2loint(big);
     const float u = (float)fma(t4, f, -(big - 6755399441055744.0));
-    const float z = u * u;
-    const float sn = u * fmaf(z, fmaf(z, fmaf(z, -0.004604428540915251f, 0.0796811580657959f), -0.6459636092185974f), 1.5707963705062866f);
-    const float cs = fmaf(z, fmaf(z, fmaf(z, -0.02042119763791561f, 0.2536039352416992f), -1.2336976528167725f), 1.0f);
-    const bool sw = q & 1;
+    const float2 cs = cis_quadrant(q, u);
     const float a = skip_att ? 1.0f : amp * rf;
-    const float re = __int_as_float(__float_as_int(sw ? sn : cs) ^ (((q + 1) & 2) << 30));
-    const float im = __int_as_float(__float_as_int(sw ? cs : sn) ^ ((q & 2) << 30));
+    const float re = cs.x, im = cs.y;
     return make_float2(a * re, a * im);
 }
 #else
@@ -562,27 +558,55 @@ struct RayleighArgs {
     double rx0[3]; double gain_lin; int skip_attenuation;
     uint64_t seed, frame_id0; uint32_t stream;
     float2* h_out; int n_ant;
+    float* sscale_out;  // as ChanArgs::sscale_out: with grid.x == 1 the CTA also writes the MRT symbol scale
 };
 
+// grid (ceil(K / 8), F) or (1, F) with sscale_out; the coefficient of (frame, antenna k, slot p) is Box-Muller of Philox
+// block (frame id, stream + (k << 8), 4 t + q), p = (2 q + e) 256 + t - the assignment of round 1, so the generated
+// channels are the same up to rounding.  Attenuation = (path amplitude of antenna k) x (1 / f per slot): the per-slot
+// reciprocals are computed once per thread and serve all antennas of the CTA.
 __global__ void __launch_bounds__(256) k_gen_rayleigh(const RayleighArgs a) {
-    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
-    const double dx = a.tx_pos[k * 3 + 0] - a.rx0[0], dy = a.tx_pos[k * 3 + 1] - a.rx0[1], dz = a.tx_pos[k * 3 + 2] - a.rx0[2];
-    const double d = sqrt(dx * dx + dy * dy + dz * dz);
-    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+    __shared__ float att_s[MAX_ANT];
+    const int per_cta = a.sscale_out ? a.n_ant : CHAN_ANT_PER_CTA;
+    const int kb = blockIdx.x * per_cta, f = blockIdx.y, t = threadIdx.x;
+    if (t < per_cta && kb + t < a.n_ant) {
+        const int k = kb + t;
+        const double dx = a.tx_pos[k * 3 + 0] - a.rx0[0], dy = a.tx_pos[k * 3 + 1] - a.rx0[1], dz = a.tx_pos[k * 3 + 2] - a.rx0[2];
+        const double d = sqrt(dx * dx + dy * dy + dz * dz);
+        att_s[t] = a.skip_attenuation ? 0.70710678118654752440f
+                                      : (float)(0.70710678118654752440 * a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846 * d));
+    }
+    float rf[8], nrm[8];
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) {
+        rf[jp] = a.skip_attenuation ? 1.0f : (float)(1.0 / a.freq_slot[jp * 256 + t]);
+        nrm[jp] = 0.f;
+    }
+    __syncthreads();
     const uint64_t fid = a.frame_id0 + f;
+    const int nk = min(per_cta, a.n_ant - kb);
+    for (int i = 0; i < nk; ++i) {
+        const int k = kb + i;
+        const float att = att_s[i];
+        float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC + t;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint32_t r[4];
-        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
-                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
-        const float2 g[2] = {box_muller(r[0], r[1]), box_muller(r[2], r[3])};
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const int p = (2 * q + e) * 256 + t;
-            float att = 0.70710678118654752440f;
-            if (!a.skip_attenuation) att *= (float)(a.gain_lin * C_LIGHT / (4.0 * 3.14159265358979323846 * d * a.freq_slot[p]));
-            out[p] = make_float2(g[e].x * att, g[e].y * att);
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r[4];
+            philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
+                          (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+            const float2 g0 = box_muller_fast(r[0], r[1]), g1 = box_muller_fast(r[2], r[3]);
+            const float s0 = att * rf[2 * q], s1 = att * rf[2 * q + 1];
+            const float2 h0 = make_float2(g0.x * s0, g0.y * s0), h1 = make_float2(g1.x * s1, g1.y * s1);
+            out[(2 * q) * 256] = h0;
+            out[(2 * q + 1) * 256] = h1;
+            // same operation order as the first pass of k_prep_realisation: bit-identical scale
+            nrm[2 * q] = fmaf(h0.x, h0.x, fmaf(h0.y, h0.y, nrm[2 * q]));
+            nrm[2 * q + 1] = fmaf(h1.x, h1.x, fmaf(h1.y, h1.y, nrm[2 * q + 1]));
         }
+    }
+    if (a.sscale_out) {
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) a.sscale_out[(size_t)f * N_SC + jp * 256 + t] = (1.0f / sqrtf(nrm[jp])) * 0.015625f;
     }
 }
 
@@ -593,43 +617,55 @@ struct CsiArgs {
     const float2* noise_in;  // [F][K][2048] injected unit normals (native slots) or nullptr -> Philox
     const float2* h_in; float2* h_out; float eps, scale;
     uint64_t seed, frame_id0; uint32_t stream; int n_ant;
+    float* sscale_out;       // as ChanArgs::sscale_out (norm of the PERTURBED rows: the precoder is derived from them)
 };
 
+// grid (K, F), or (1, F) with sscale_out: the CTA walks all antennas of the realisation and also writes the symbol scale
 __global__ void __launch_bounds__(256) k_csi_error(const CsiArgs a) {
     __shared__ double red_s[8];
-    const int k = blockIdx.x, f = blockIdx.y, t = threadIdx.x;
-    const float2* in = a.h_in + ((size_t)f * a.n_ant + k) * N_SC;
-    float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
-    float2 h[8];
-    double pw = 0.0;
+    const int f = blockIdx.y, t = threadIdx.x;
+    const int k0 = a.sscale_out ? 0 : blockIdx.x, k1 = a.sscale_out ? a.n_ant : blockIdx.x + 1;
+    const uint64_t fid = a.frame_id0 + f;
+    float nrm[8];
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) {
-        h[jp] = in[jp * 256 + t];
-        pw += (double)h[jp].x * h[jp].x + (double)h[jp].y * h[jp].y;
-    }
-    pw = block_sum_256(pw, red_s, t) / N_SC;
-    const float sig = a.eps * (float)sqrt(0.5 * pw);
-    if (a.noise_in) {
-        const float2* nz = a.noise_in + ((size_t)f * a.n_ant + k) * N_SC;
+    for (int jp = 0; jp < 8; ++jp) nrm[jp] = 0.f;
+    for (int k = k0; k < k1; ++k) {
+        const float2* in = a.h_in + ((size_t)f * a.n_ant + k) * N_SC;
+        float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
+        float2 h[8];
+        double pw = 0.0;
 #pragma unroll
         for (int jp = 0; jp < 8; ++jp) {
-            const float2 g = nz[jp * 256 + t];
-            out[jp * 256 + t] = make_float2(fmaf(a.scale, h[jp].x, sig * g.x), fmaf(a.scale, h[jp].y, sig * g.y));
+            h[jp] = in[jp * 256 + t];
+            pw += (double)h[jp].x * h[jp].x + (double)h[jp].y * h[jp].y;
         }
-        return;
+        pw = block_sum_256(pw, red_s, t) / N_SC;
+        const float sig = a.eps * (float)sqrt(0.5 * pw);
+        float2 g[8];
+        if (a.noise_in) {
+            const float2* nz = a.noise_in + ((size_t)f * a.n_ant + k) * N_SC;
+#pragma unroll
+            for (int jp = 0; jp < 8; ++jp) g[jp] = nz[jp * 256 + t];
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t r[4];
+                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
+                              (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
+                g[2 * q] = box_muller_fast(r[0], r[1]);
+                g[2 * q + 1] = box_muller_fast(r[2], r[3]);
+            }
+        }
+#pragma unroll
+        for (int jp = 0; jp < 8; ++jp) {
+            const float2 o = make_float2(fmaf(a.scale, h[jp].x, sig * g[jp].x), fmaf(a.scale, h[jp].y, sig * g[jp].y));
+            out[jp * 256 + t] = o;
+            nrm[jp] = fmaf(o.x, o.x, fmaf(o.y, o.y, nrm[jp]));  // operation order of k_prep_realisation's first pass
+        }
     }
-    const uint64_t fid = a.frame_id0 + f;
+    if (a.sscale_out) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        uint32_t r[4];
-        philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
-                      (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
-        const float2 g[2] = {box_muller(r[0], r[1]), box_muller(r[2], r[3])};
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const int jp = 2 * q + e;
-            out[jp * 256 + t] = make_float2(fmaf(a.scale, h[jp].x, sig * g[e].x), fmaf(a.scale, h[jp].y, sig * g[e].y));
-        }
+        for (int jp = 0; jp < 8; ++jp) a.sscale_out[(size_t)f * N_SC + jp * 256 + t] = (1.0f / sqrtf(nrm[jp])) * 0.015625f;
     }
 }
 

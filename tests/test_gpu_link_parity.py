@@ -279,20 +279,23 @@ def test_cnc_loop_kernel_matches_single_kernel_form(monkeypatch):
             eng.close()
 
 
-def test_fused_norm_pass_is_bit_identical(engine):
-    """From 2 realisations per SM on, k_gen_channel writes the MRT symbol scale itself (one CTA per realisation) and
-    k_prep_realisation skips its norm pass; below that the realisation kernel computes it.  Same operation order, so a
-    large batch and the same frames run as small batches give exactly the same counters and samples.  (Two-path channel: a
-    line-of-sight channel goes through the closed-form k_prep_los at every batch size.)"""
-    engine.configure(n_ant=16, channel="two_path", pa="softlim", ibo_db=0.0, receiver="mcnc")
+@pytest.mark.parametrize("channel,csi_eps", [("two_path", 0.0), ("rayleigh", 0.0), ("los", 0.2), ("two_path", 0.1)])
+def test_fused_norm_pass_is_bit_identical(engine, channel, csi_eps):
+    """From 2 realisations per SM on, the kernel that writes the rows the precoder is derived from (k_gen_channel,
+    k_gen_rayleigh, or k_csi_error for a channel with CSI error) also writes the MRT symbol scale (one CTA per realisation)
+    and k_prep_realisation skips its norm pass; below that the realisation kernel computes it.  Same operation order, so a
+    large batch and the same frames run as small batches give exactly the same counters and samples.  (A line-of-sight
+    channel without CSI error goes through the closed-form k_prep_los at every batch size.)"""
+    engine.configure(n_ant=16, channel=channel, pa="softlim", ibo_db=0.0, receiver="mcnc")
     n, n_iter = 320, 2                      # 320 >= 2 * 148: fused path
-    big = engine.simulate(n, n_iter, 16.0, seed=9, frame_id0=500, dumps=("rx_eq",))
+    big = engine.simulate(n, n_iter, 16.0, seed=9, frame_id0=500, csi_eps=csi_eps, dumps=("rx_eq",))
     err = np.zeros_like(big["err"])
     for c0 in range(0, n, 80):              # 80 < 2 * 148: norm pass in the realisation kernel
-        part = engine.simulate(80, n_iter, 16.0, seed=9, frame_id0=500 + c0, dumps=("rx_eq",))
+        part = engine.simulate(80, n_iter, 16.0, seed=9, frame_id0=500 + c0, csi_eps=csi_eps, dumps=("rx_eq",))
         err += part["err"]
         assert np.array_equal(part["rx_eq"], big["rx_eq"][c0:c0 + 80])
     assert np.array_equal(err, big["err"])
+    assert err[0] > 0
 
 
 def test_closed_form_los_realisation_matches_oracle(monkeypatch):
