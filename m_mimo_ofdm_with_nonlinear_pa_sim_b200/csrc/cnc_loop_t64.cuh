@@ -18,15 +18,20 @@ namespace mmimo {
 #ifndef CNC_SPLIT
 #define CNC_SPLIT 1  // 0: CNC frames stay entirely in k_link_frame_t64 (round-2 form)
 #endif
-constexpr int CNC_LOOP_SMEM_BYTES = (4096 + R64_GROUPS * t64::XBUF) * 8;
+constexpr int CNC_LOOP_SMEM_BYTES = (4096 + R64_GROUPS * (t64::XBUF + N_SC)) * 8;  // table + per group: exchange buffer, received signal
+static_assert(CNC_LOOP_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CTA");
 
 template <int PA>
-__global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs a, const float2* __restrict__ tab_g) {
+// uni_ss / uni_agc: the loop side's symbol scale and 1 / (64 alpha) when they are the same for every sub-carrier (they are for
+// CncReceiver: h = v = 1, corrector.py:104-107); uniform == 0 reads a.loop.sscale / a.loop.agc_inv per slot instead.
+__global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs a, const float2* __restrict__ tab_g, const int uniform,
+                                                                 const float uni_ss, const float2 uni_agc) {
     extern __shared__ __align__(128) float2 smem[];
     float2* tab = smem;
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
     pf2* buf = reinterpret_cast<pf2*>(smem + 4096) + g * t64::XBUF;
     float2* sym_s = reinterpret_cast<float2*>(buf) + N_SC;  // scaled symbols of the coming regeneration (idle half of the buffer)
+    float2* rx_s = smem + 4096 + R64_GROUPS * t64::XBUF + g * N_SC + lane;  // equalised received signal of the group's frame
     const SyncGroup sy{g + 1};
     for (int i = t; i < t64::TAB_FLOAT2; i += FFT_THREADS) tab[i] = tab_g[i];
     __syncthreads();
@@ -76,7 +81,11 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
                 txw[i >> 2] |= ((blk[i & 3][jp >> 2] >> (8 * (jp & 3))) & 0xffu) << (8 * (i & 3));
             }
         }
-        const float2* __restrict__ rxe = a.rx_eq_in + (size_t)f * N_SC + lane;
+        {   // every thread reads back only what it wrote: no barrier needed
+            const float2* __restrict__ rxe = a.rx_eq_in + (size_t)f * N_SC + lane;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) rx_s[64 * i] = rxe[64 * i];
+        }
         const float2* __restrict__ ai = sd.agc_inv + f * sd.agc_fs + lane;
         const float* __restrict__ ss = sd.sscale + f * sd.sscale_fs + lane;
         const float p0 = sc.pa_p0_loop;
@@ -136,13 +145,13 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
             for (int w = 0; w < 8; ++w) detw[w] = 0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                float2 corr = rxe[64 * i];
+                float2 corr = rx_s[64 * i];
                 if (pass > 0) {
                     const int n1 = i < 16 ? i : i + 32;
                     pf2 yv = x[rev64(n1)];
                     if (i == 0 && lane == 0) yv = x[rev64(16)];
                     if (T64_PA_UNIT) yv = pmul(yv, pbc(pa_out_scale));
-                    const float2 z = cmul(unpk(yv), ai[64 * i]);
+                    const float2 z = cmul(unpk(yv), uniform ? uni_agc : ai[64 * i]);
                     const float2 sy0 = qam_symbol(a.qam, (curw[i >> 2] >> (8 * (i & 3))) & 0xffu);
                     const float2 d = csub(z, sy0);  // distortion estimate, corrector.py:110
                     corr = csub(corr, d);           // corrector.py:74
@@ -170,7 +179,7 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const float2 s = qam_symbol(a.qam, (detw[i >> 2] >> (8 * (i & 3))) & 0xffu);
-                    const float gsc = ss[64 * i] * pa_in_scale;
+                    const float gsc = (uniform ? uni_ss : ss[64 * i]) * pa_in_scale;
                     sym_s[lane + 64 * i] = make_float2(s.x * gsc, s.y * gsc);
                 }
             }

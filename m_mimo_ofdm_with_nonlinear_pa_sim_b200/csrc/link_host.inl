@@ -224,9 +224,10 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         return 1;
     if (want_det && c->det.reserve(chunk * (I + 1) * N_SC)) return 1;
     if (want_corr && c->corr.reserve(chunk * (I + 1) * N_SC * 8)) return 1;
+    double cnc_alpha = 1.0;
     if (!mcnc) {
         if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 4) || c->cnc_agc_inv.reserve(N_SC * 8)) return 1;
-        const double alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
+        const double alpha = cnc_alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
         k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_ones.as<float2>(), make_float2(1.f, 0.f), N_SC);
         k_fill_f<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float>(), 1.f / 64.f, N_SC);
         k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_agc_inv.as<float2>(), make_float2((float)(1.0 / (64.0 * alpha)), 0.f), N_SC);
@@ -383,23 +384,24 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
             if (f2.err_out) CK(cudaMemsetAsync(c->err.p, 0, (size_t)n * (I + 1) * 4, c->stream));
         }
         const int grid2 = std::min((n + R64_GROUPS - 1) / R64_GROUPS, c->n_sm);
+        const float2 cnc_agc_uni = make_float2((float)(1.0 / (64.0 * cnc_alpha)), 0.f);  // what k_fill_c wrote into cnc_agc_inv
         prof_begin(c, PROF_FRAME);
         switch (cfg.pa_kind) {
             case MMIMO_PA_NONE:
                 launch_frame<PA_NONE>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
                 break;
             case MMIMO_PA_SOFT_LIMITER:
                 launch_frame<PA_SOFT_LIMITER>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
                 break;
             case MMIMO_PA_RAPP:
                 launch_frame<PA_RAPP>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
                 break;
             default:
                 launch_frame<PA_TOI>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>());
+                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
                 break;
         }
         prof_end(c);
