@@ -24,8 +24,12 @@ static_assert(CNC_LOOP_SMEM_BYTES <= 227 * 1024, "shared-memory budget of one CT
 template <int PA>
 // uni_ss / uni_agc: the loop side's symbol scale and 1 / (64 alpha) when they are the same for every sub-carrier (they are for
 // CncReceiver: h = v = 1, corrector.py:104-107); uniform == 0 reads a.loop.sscale / a.loop.agc_inv per slot instead.
+// mode bit 0: two-user batch, frames are receiver instances (realisation, user) and user 1 counts at err_total[32 + pass];
+// mode bit 1: CncMuReceiver (corrector.py:288-345): the regenerated signal is v (detected symbol) + v (TRUE symbol of the other
+// user, instance f ^ 1) with the explicit loop-side precoder a.loop.v (uni_v when uniform: sqrt(2)/2, corrector.py:322).
 __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs a, const float2* __restrict__ tab_g, const int uniform,
-                                                                 const float uni_ss, const float2 uni_agc) {
+                                                                 const float uni_ss, const float2 uni_agc, const int mode,
+                                                                 const float2 uni_v) {
     extern __shared__ __align__(128) float2 smem[];
     float2* tab = smem;
     const int t = threadIdx.x, lane = t & 63, g = t >> 6;
@@ -53,34 +57,36 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
         }
         const FrameScalars sc = a.scal[f * a.scal_fs];
         // symbol values of the 32 slots lane + 64 i: byte i & 3 of word i >> 2.  Slot p belongs to Philox block p & 255, byte p >> 8
-        uint32_t txw[8], curw[8];
-        if (a.tx_idx) {
-            const uint8_t* p = a.tx_idx + (size_t)f * N_SC + lane;
+        uint32_t txw[8], curw[8], otw[8];
+        auto load_tx32 = [&](const int inst, uint32_t (&w)[8]) {
 #pragma unroll
-            for (int w = 0; w < 8; ++w) txw[w] = 0;
+            for (int q = 0; q < 8; ++q) w[q] = 0;
+            if (a.tx_idx) {
+                const uint8_t* p = a.tx_idx + (size_t)inst * N_SC + lane;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) txw[i >> 2] |= (uint32_t)p[64 * i] << (8 * (i & 3));
-        } else {
-            const uint64_t fid = a.frame_id0 + f;
-            const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
-            const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
-            uint32_t blk[4][2];
+                for (int i = 0; i < 32; ++i) w[i >> 2] |= (uint32_t)p[64 * i] << (8 * (i & 3));
+            } else {
+                const uint64_t fid = a.frame_id0 + inst;
+                const uint32_t m = (1u << (2 * a.qam.log2side)) - 1u;
+                const uint32_t m4 = m | (m << 8) | (m << 16) | (m << 24);
+                uint32_t blk[4][2];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                uint32_t r[4];
-                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)(lane + 64 * q), (uint32_t)a.seed,
-                              (uint32_t)(a.seed >> 32), r);
-                blk[q][0] = r[0] & m4;
-                blk[q][1] = r[1] & m4;
+                for (int q = 0; q < 4; ++q) {
+                    uint32_t r[4];
+                    philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), RNG_BITS, (uint32_t)(lane + 64 * q), (uint32_t)a.seed,
+                                  (uint32_t)(a.seed >> 32), r);
+                    blk[q][0] = r[0] & m4;
+                    blk[q][1] = r[1] & m4;
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {  // slot lane + 64 i: block i & 3, byte jp = i >> 2 of its two words
+                    const int jp = i >> 2;
+                    w[i >> 2] |= ((blk[i & 3][jp >> 2] >> (8 * (jp & 3))) & 0xffu) << (8 * (i & 3));
+                }
             }
-#pragma unroll
-            for (int w = 0; w < 8; ++w) txw[w] = 0;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {  // slot lane + 64 i: block i & 3, byte jp = i >> 2 of its two words
-                const int jp = i >> 2;
-                txw[i >> 2] |= ((blk[i & 3][jp >> 2] >> (8 * (jp & 3))) & 0xffu) << (8 * (i & 3));
-            }
-        }
+        };
+        load_tx32(f, txw);
+        if (mode & 2) load_tx32(f ^ 1, otw);
         {   // every thread reads back only what it wrote: no barrier needed
             const float2* __restrict__ rxe = a.rx_eq_in + (size_t)f * N_SC + lane;
 #pragma unroll
@@ -92,7 +98,8 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
         const float sqrt_p0 = sqrtf(p0);
         const float pa_out_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? 1.0f / sqrt_p0 : sqrt_p0;
         const float pa_in_scale = !T64_PA_UNIT || PA == PA_NONE ? 1.0f : PA == PA_TOI ? sqrt_p0 : 1.0f / sqrt_p0;
-        const size_t cnt0 = a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u;
+        const size_t cnt0 = (a.fpp ? 64u * ((a.frame0 + (unsigned)f) / (unsigned)a.fpp) : 0u) + ((mode & 1) ? (f & 1) * 32 : 0);
+        const float g_oth = (mode & 2) ? (uniform ? uni_ss : sd.sscale[f * sd.sscale_fs]) * pa_in_scale : 0.f;
 
         for (int pass = 0; pass <= a.n_iter; ++pass) {
             pf2 x[64];
@@ -180,7 +187,15 @@ __global__ void __launch_bounds__(FFT_THREADS, 1) k_cnc_loop_t64(const FrameArgs
                 for (int i = 0; i < 32; ++i) {
                     const float2 s = qam_symbol(a.qam, (detw[i >> 2] >> (8 * (i & 3))) & 0xffu);
                     const float gsc = (uniform ? uni_ss : ss[64 * i]) * pa_in_scale;
-                    sym_s[lane + 64 * i] = make_float2(s.x * gsc, s.y * gsc);
+                    float2 xs = make_float2(s.x * gsc, s.y * gsc);
+                    if (mode & 2) {  // frame kernel, two users on an explicit-precoder side: v * s, then + v_other * s_other
+                        const int p = lane + 64 * i;
+                        const float2 v = uniform ? uni_v : sd.v[f * sd.v_fs + p];
+                        const float2 vo = uniform ? uni_v : sd.v[(f ^ 1) * sd.v_fs + p];
+                        const float2 o = qam_symbol(a.qam, (otw[i >> 2] >> (8 * (i & 3))) & 0xffu);
+                        xs = unpk(pcfma(pk2(vo), pk(o.x * g_oth, o.y * g_oth), pcmul(pk2(v), xs.x, xs.y)));
+                    }
+                    sym_s[lane + 64 * i] = xs;
                 }
             }
         }

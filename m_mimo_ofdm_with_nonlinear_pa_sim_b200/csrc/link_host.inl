@@ -389,19 +389,19 @@ static int run_link(mmimo_ctx* c, const mmimo_sim_request* rq, mmimo_sim_result*
         switch (cfg.pa_kind) {
             case MMIMO_PA_NONE:
                 launch_frame<PA_NONE>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
+                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni, 0, make_float2(1.f, 0.f));
                 break;
             case MMIMO_PA_SOFT_LIMITER:
                 launch_frame<PA_SOFT_LIMITER>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
+                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni, 0, make_float2(1.f, 0.f));
                 break;
             case MMIMO_PA_RAPP:
                 launch_frame<PA_RAPP>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
+                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni, 0, make_float2(1.f, 0.f));
                 break;
             default:
                 launch_frame<PA_TOI>(fa, c, grid);
-                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni);
+                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, cnc_agc_uni, 0, make_float2(1.f, 0.f));
                 break;
         }
         prof_end(c);

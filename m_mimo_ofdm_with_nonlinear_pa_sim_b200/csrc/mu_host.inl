@@ -102,6 +102,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
         c->launches++;
 
         FrameArgs fa{};
+        double cnc_alpha = 1.0;
         const long long hfs = (long long)K * N_SC;
         fa.tx.h_mac = h; fa.tx.h_mac_fs = hfs;
         fa.tx.h_pre = h; fa.tx.h_pre_fs = hfs;
@@ -115,7 +116,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             // single-antenna model of the transmitter (corrector.py:52-112, :288-345): h = 1, estimate / alpha; CncMuReceiver
             // adds the other user's true symbols with equal power: explicit "precoder" rows sqrt(2)/2 for both users
             if (c->cnc_ones.reserve(N_SC * 8) || c->cnc_v.reserve(N_SC * 4) || c->cnc_agc_inv.reserve(N_SC * 8) || c->s_a.reserve(N_SC * 8)) return 1;
-            const double alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
+            const double alpha = cnc_alpha = (cfg.pa_kind == MMIMO_PA_TOI || cfg.pa_kind == MMIMO_PA_NONE) ? 1.0 : calc_alpha_host(cfg.ibo_db);
             k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_ones.as<float2>(), make_float2(1.f, 0.f), N_SC);
             k_fill_f<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_v.as<float>(), 1.f / 64.f, N_SC);
             k_fill_c<<<nblk(N_SC), 256, 0, c->stream>>>(c->cnc_agc_inv.as<float2>(), make_float2((float)(1.0 / (64.0 * alpha)), 0.f), N_SC);
@@ -175,15 +176,41 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
         fa.rx_eq_out = (rs->rx_eq && !rq->rx_eq_in) ? c->rx_eq.as<float2>() : nullptr;
         fa.err_total = counters;
         fa.rxeq_scratch = c->rxeq_scr.as<float2>();
+        // CncReceiver / CncMuReceiver per user: the two-user frame kernel runs the real transmission only, the receiver loops
+        // run one instance per 64-thread group in k_cnc_loop_t64 (cnc_loop_t64.cuh); identical decisions and counters
+        const bool cnc_rx = rq->receiver == MMIMO_MU_RX_CNC || rq->receiver == MMIMO_MU_RX_CNC_MU;
+        const bool cnc_split = cnc_rx && c->cnc_split && c->frame_kernel == 0 && I > 0;
+        FrameArgs f2 = fa;
+        if (cnc_split) {
+            f2.rx_eq_in = c->rx_eq.as<float2>();
+            fa.n_iter = 0; fa.det_out = nullptr; fa.err_total = nullptr;
+            fa.rx_eq_out = rq->rx_eq_in ? nullptr : c->rx_eq.as<float2>();
+        }
+        const int grid2 = std::min((ni + R64_GROUPS - 1) / R64_GROUPS, c->n_sm);
+        const int mode2 = rq->receiver == MMIMO_MU_RX_CNC_MU ? 3 : 1;
+        const float2 uv = make_float2(0.70710678118654752440f, 0.f), uagc = make_float2((float)(1.0 / (64.0 * cnc_alpha)), 0.f);
         prof_begin(c, PROF_FRAME);
+        const bool pass0 = !(cnc_split && rq->rx_eq_in);  // a receiver-only call has its equalised signal already
         switch (cfg.pa_kind) {
-            case MMIMO_PA_NONE: launch_frame_mu<PA_NONE>(fa, c, ni); break;
-            case MMIMO_PA_SOFT_LIMITER: launch_frame_mu<PA_SOFT_LIMITER>(fa, c, ni); break;
-            case MMIMO_PA_RAPP: launch_frame_mu<PA_RAPP>(fa, c, ni); break;
-            default: launch_frame_mu<PA_TOI>(fa, c, ni); break;
+            case MMIMO_PA_NONE:
+                if (pass0) launch_frame_mu<PA_NONE>(fa, c, ni);
+                if (cnc_split) k_cnc_loop_t64<PA_NONE><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, uagc, mode2, uv);
+                break;
+            case MMIMO_PA_SOFT_LIMITER:
+                if (pass0) launch_frame_mu<PA_SOFT_LIMITER>(fa, c, ni);
+                if (cnc_split) k_cnc_loop_t64<PA_SOFT_LIMITER><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, uagc, mode2, uv);
+                break;
+            case MMIMO_PA_RAPP:
+                if (pass0) launch_frame_mu<PA_RAPP>(fa, c, ni);
+                if (cnc_split) k_cnc_loop_t64<PA_RAPP><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, uagc, mode2, uv);
+                break;
+            default:
+                if (pass0) launch_frame_mu<PA_TOI>(fa, c, ni);
+                if (cnc_split) k_cnc_loop_t64<PA_TOI><<<grid2, FFT_THREADS, CNC_LOOP_SMEM_BYTES, c->stream>>>(f2, c->tw_t64.as<float2>(), 1, 1.f / 64.f, uagc, mode2, uv);
+                break;
         }
         prof_end(c);
-        c->launches++;
+        c->launches += (pass0 ? 1 : 0) + (cnc_split ? 1 : 0);
         CK(cudaGetLastError());
 
         if (rs->det && download_native<uint8_t>(c, c->det.as<uint8_t>(), rs->det + i0 * (I + 1) * N_SC, (size_t)ni * (I + 1))) return 1;

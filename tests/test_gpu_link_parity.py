@@ -203,6 +203,13 @@ def test_multi_point_sweep_equals_point_by_point(engine):
     e2 = engine.sweep(snr[:2], None, fpp, n_iter, seed=5)
     r0 = engine.simulate(fpp, n_iter, float(snr[0]), seed=5, frame_id0=0)["err"]
     assert np.array_equal(e2[0], r0)
+    # CncReceiver points (per-point Eb/N0 only): the receiver loop runs in k_cnc_loop_t64, which counts per point as well;
+    # 23 frames per point leave groups of the last CTA round without a frame and put point boundaries inside a CTA
+    engine.configure(n_ant=8, channel="los", pa="softlim", ibo_db=1.0, receiver="cnc")
+    e3 = engine.sweep(snr[:3], None, 23, n_iter, seed=6, frame_id0=40)
+    for p in range(3):
+        ref = engine.simulate(23, n_iter, float(snr[p]), seed=6, frame_id0=40 + p * 23)["err"]
+        assert np.array_equal(e3[p], ref), (p, e3[p], ref)
 
 
 def test_radix64_and_radix16_frame_kernels_agree(monkeypatch):

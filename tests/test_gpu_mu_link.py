@@ -140,3 +140,29 @@ def test_mu_k64_full_frame_vs_reference(engine, tag):
         assert rel_l2(out["agc"][0, u], g["agc_sc_%s_u%d" % (tag, u)]) < TOL
         assert rel_l2(out["rx_eq"][0, u], g["rx_eq_sc_%s_u%d" % (tag, u)]) < 2 * TOL
         check_user("mu K=64 %s frame" % tag, out, u, ref, g["det_%s_u%d" % (tag, u)], g["err_%s_u%d" % (tag, u)], g["iters"])
+
+
+def test_mu_cnc_loop_kernel_matches_single_kernel_form(monkeypatch):
+    """Two-user runs with the single-antenna receivers (CncReceiver, CncMuReceiver): pass 0 in the two-user frame kernel + the
+    receiver loops in k_cnc_loop_t64 (one instance per 64-thread group, the default) against whole instances in the frame
+    kernel (MMIMO_CNC_SPLIT=0): identical decisions and counters of both users, odd realisation counts included."""
+    from m_mimo_ofdm_with_nonlinear_pa_sim_b200 import LinkEngine
+    engines = {}
+    try:
+        for split in ("1", "0"):
+            monkeypatch.setenv("MMIMO_CNC_SPLIT", split)
+            engines[split] = LinkEngine(0)
+        monkeypatch.delenv("MMIMO_CNC_SPLIT", raising=False)
+        for receiver, tag, pa, n_ant, n_real, n_iter in (("cnc", "mrt", "softlim", 8, 7, 3), ("cnc_mu", "zf", "softlim", 16, 301, 2),
+                                                         ("cnc_mu", "mrt", "rapp", 4, 5, 4), ("cnc", "zf", "toi", 64, 75, 5)):
+            outs = {}
+            for split, eng in engines.items():
+                eng.configure(n_ant=n_ant, channel="los", pa=pa, ibo_db=1.0, receiver="mcnc")
+                outs[split] = eng.mu_simulate(n_real, n_iter, 18.0, precoding=tag, receiver=receiver, seed=23, dumps=("det", "rx_eq"))
+            a, b = outs["1"], outs["0"]
+            for key in ("err", "det", "rx_eq"):
+                assert np.array_equal(a[key], b[key]), (receiver, tag, pa, key)
+            assert a["err"].sum() > 0
+    finally:
+        for eng in engines.values():
+            eng.close()
