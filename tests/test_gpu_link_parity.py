@@ -19,7 +19,7 @@ GOLDEN_4096 = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayl
                "link_k8_los_rapp",
                # the headline shape with 32 frames and its CNC twin with 16 (tests/golden/make_golden_k64.py)
                "link_k64_los_mcnc32", "link_k64_los_cnc16"]
-# Frames that may hit a sub-margin decision, per case.  Measured on the B200 (profiles/r02_margin_histogram.json): of 1.5 M
+# Frames that may hit a sub-margin decision, per case.  Measured on the B200 (profiles/r02_margin_histogram.json): of 1.35 M
 # decisions compared over all cases NONE differed from the reference, although the oracle's slicer input came as close as
 # 5e-7 to a boundary; the allowance below is slack for other inputs, the rule itself (parity_util.check_frame: a differing
 # decision must sit within MARGIN of a boundary) is never relaxed.
