@@ -98,7 +98,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
         mp.avg_sample_power = mp.avg_symbol_power * ((double)cfg.n_sub_carr / cfg.n_fft);
         mp.snr_lin = pow(10.0, rq->snr_db / 10.0);
         mp.loop_cnc = rq->receiver == MMIMO_MU_RX_CNC || rq->receiver == MMIMO_MU_RX_CNC_MU;
-        k_prep_mu<<<nr, 256, 0, c->stream>>>(mp);
+        k_prep_mu<<<nr, MU_T, 0, c->stream>>>(mp);
         c->launches++;
 
         FrameArgs fa{};

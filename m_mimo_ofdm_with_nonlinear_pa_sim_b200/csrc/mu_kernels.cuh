@@ -20,11 +20,14 @@ struct MuPrepArgs {
     double ibo_lin, avg_symbol_power, avg_sample_power, snr_lin;
 };
 
-__global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // two CTAs per SM: the coefficients c.. are spilled around the last pass
-    __shared__ float part_s[MAX_ANT][8];
+// 512 threads, four sub-carrier slots per thread (MU_NS): half the fp64 accumulators per thread of the 256 x 8 form, so that two
+// CTAs = 1024 threads per SM are resident and twice as many row loads are in flight
+constexpr int MU_T = 512, MU_NS = N_SC / MU_T, MU_W = MU_T / 32;
+__global__ void __launch_bounds__(MU_T, 2) k_prep_mu(const MuPrepArgs a) {
+    __shared__ float part_s[MAX_ANT][MU_W];
     __shared__ float alpha_s[MAX_ANT];
     __shared__ double vkpow_s[MAX_ANT];
-    __shared__ double red_s[8];
+    __shared__ double red_s[MU_W];
     const int r = blockIdx.x, t = threadIdx.x, K = a.n_ant;
     const float2* __restrict__ H0 = a.h + (size_t)(2 * r) * K * N_SC;
     const float2* __restrict__ H1 = H0 + (size_t)K * N_SC;
@@ -32,13 +35,13 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
     float2* V1 = V0 + (size_t)K * N_SC;
 
     // per sub-carrier Gram matrix of T = [h_0 h_1] (K x 2): G[a][b] = sum_k h_a conj(h_b)   (antenna_array.py:236-240)
-    double g00[8], g11[8], g01r[8], g01i[8];
+    double g00[MU_NS], g11[MU_NS], g01r[MU_NS], g01i[MU_NS];
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) g00[jp] = g11[jp] = g01r[jp] = g01i[jp] = 0.0;
+    for (int jp = 0; jp < MU_NS; ++jp) g00[jp] = g11[jp] = g01r[jp] = g01i[jp] = 0.0;
     for (int k = 0; k < K; ++k) {
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
-            const float2 x = H0[(size_t)k * N_SC + jp * 256 + t], y = H1[(size_t)k * N_SC + jp * 256 + t];
+        for (int jp = 0; jp < MU_NS; ++jp) {
+            const float2 x = H0[(size_t)k * N_SC + jp * MU_T + t], y = H1[(size_t)k * N_SC + jp * MU_T + t];
             g00[jp] += (double)x.x * x.x + (double)x.y * x.y;
             g11[jp] += (double)y.x * y.x + (double)y.y * y.y;
             g01r[jp] += (double)x.x * y.x + (double)x.y * y.y;   // x conj(y)
@@ -46,9 +49,9 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
         }
     }
     // per sub-carrier coefficients: v_0 = c00 conj(h_0) + c10 conj(h_1), v_1 = c01 conj(h_0) + c11 conj(h_1)
-    double c00[8], c11[8], c01r[8], c01i[8];  // c10 = conj(c01); c00, c11 real
+    double c00[MU_NS], c11[MU_NS], c01r[MU_NS], c01i[MU_NS];  // c10 = conj(c01); c00, c11 real
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) {
+    for (int jp = 0; jp < MU_NS; ++jp) {
         if (a.precoding == MU_MRT) {  // common normalisation over users, antenna_array.py:202-220
             c00[jp] = c11[jp] = 1.0 / sqrt(g00[jp] + g11[jp]);
             c01r[jp] = c01i[jp] = 0.0;
@@ -80,8 +83,8 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
     for (int k = 0; k < K; ++k) {
         float pw = 0.f;
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
-            const int p = jp * 256 + t;
+        for (int jp = 0; jp < MU_NS; ++jp) {
+            const int p = jp * MU_T + t;
             const float2 x = H0[(size_t)k * N_SC + p], y = H1[(size_t)k * N_SC + p];
             // v_0 = c00 conj(h_0) + conj(c01) conj(h_1),  v_1 = c01 conj(h_0) + c11 conj(h_1); formed in double: the two
             // terms of a zero-forcing precoder nearly cancel
@@ -102,7 +105,7 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
     if (t < K) {
         double s = 0.0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) s += (double)part_s[t][w];
+        for (int w = 0; w < MU_W; ++w) s += (double)part_s[t][w];
         vkpow_s[t] = s;
         const double g2 = a.ibo_lin * (double)N_SC / (s * (double)K);   // corrector.py:390-394
         const double g = sqrt(g2);
@@ -116,16 +119,16 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
     //   S00 = sum_k alpha_k |h_0|^2, S11 = sum_k alpha_k |h_1|^2, S01 = sum_k alpha_k h_0 conj(h_1):
     //   a_0 = c00 S00 + conj(c01) S01,   a_1 = c01 conj(S01) + c11 S11
     // - one more pass over the channel rows only (the precoder rows are not read back: 4.4 GB less per 2072 realisations)
-    double a0r[8], a0i[8], a1r[8], a1i[8];
+    double a0r[MU_NS], a0i[MU_NS], a1r[MU_NS], a1i[MU_NS];
     {
-        double s00[8], s11[8], s01r[8], s01i[8];
+        double s00[MU_NS], s11[MU_NS], s01r[MU_NS], s01i[MU_NS];
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) s00[jp] = s11[jp] = s01r[jp] = s01i[jp] = 0.0;
+        for (int jp = 0; jp < MU_NS; ++jp) s00[jp] = s11[jp] = s01r[jp] = s01i[jp] = 0.0;
         for (int k = 0; k < K; ++k) {
             const double al = alpha_s[k];
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) {
-                const int p = jp * 256 + t;
+            for (int jp = 0; jp < MU_NS; ++jp) {
+                const int p = jp * MU_T + t;
                 const float2 x = H0[(size_t)k * N_SC + p], y = H1[(size_t)k * N_SC + p];
                 s00[jp] += al * ((double)x.x * x.x + (double)x.y * x.y);
                 s11[jp] += al * ((double)y.x * y.x + (double)y.y * y.y);
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
             }
         }
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
+        for (int jp = 0; jp < MU_NS; ++jp) {
             a0r[jp] = c00[jp] * s00[jp] + (c01r[jp] * s01r[jp] + c01i[jp] * s01i[jp]);   // conj(c01) S01
             a0i[jp] = c01r[jp] * s01i[jp] - c01i[jp] * s01r[jp];
             a1r[jp] = (c01r[jp] * s01r[jp] + c01i[jp] * s01i[jp]) + c11[jp] * s11[jp];   // c01 conj(S01)
@@ -143,16 +146,16 @@ __global__ void __launch_bounds__(256, 2) k_prep_mu(const MuPrepArgs a) {  // tw
     }
     double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) {
-        const int p = jp * 256 + t;
+    for (int jp = 0; jp < MU_NS; ++jp) {
+        const int p = jp * MU_T + t;
         const double a0 = a0r[jp] * a0r[jp] + a0i[jp] * a0i[jp];
         const double a1 = a1r[jp] * a1r[jp] + a1i[jp] * a1i[jp];
         s0 += a0; s1 += a1;
         a.agc_inv[(size_t)(2 * r) * N_SC + p] = make_float2((float)(a0r[jp] / (64.0 * a0)), (float)(-a0i[jp] / (64.0 * a0)));
         a.agc_inv[(size_t)(2 * r + 1) * N_SC + p] = make_float2((float)(a1r[jp] / (64.0 * a1)), (float)(-a1i[jp] / (64.0 * a1)));
     }
-    s0 = block_sum_256(s0, red_s, t);
-    s1 = block_sum_256(s1, red_s, t);
+    s0 = block_sum_n<MU_W>(s0, red_s, t);
+    s1 = block_sum_n<MU_W>(s1, red_s, t);
     if (t == 0) {
         double tot = 0.0;
         for (int k = 0; k < K; ++k) tot += vkpow_s[k];

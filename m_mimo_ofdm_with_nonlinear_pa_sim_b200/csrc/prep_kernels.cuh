@@ -271,6 +271,19 @@ __device__ __forceinline__ double block_sum_256(double v, double* red_s, int t) 
     return s;
 }
 
+template <int NW>
+__device__ __forceinline__ double block_sum_n(double v, double* red_s, int t) {  // NW warps
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((t & 31) == 0) red_s[t >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) s += red_s[w];
+    return s;
+}
+
 template <bool SWEEP>
 __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, const SweepArgs sw) {
     __shared__ float part_s[MAX_ANT][8];
