@@ -133,7 +133,7 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
         sscale_ready = n >= 2 * c->n_sm;
         xa.sscale_out = sscale_ready ? c->sscale.as<float>() : nullptr;
         prof_begin(c, PROF_CHAN);
-        k_csi_error<<<dim3(sscale_ready ? 1 : K, n), 256, 0, c->stream>>>(xa);
+        k_csi_error<<<dim3(sscale_ready ? 1 : K, n), CSI_T, 0, c->stream>>>(xa);
         prof_end(c);
         c->launches++;
     }
@@ -178,8 +178,8 @@ static int run_realisation(mmimo_ctx* c, const mmimo_sim_request* rq, const Real
     pa.snr_lin = pow(10.0, rq->snr_db / 10.0);
     SweepArgs sw{c->sweep.snr_lin, c->sweep.ibo_lin, c->sweep.fpp, (unsigned)c0, sscale_ready};
     prof_begin(c, PROF_PREP);
-    if (sw.fpp) k_prep_realisation<true><<<n, 256, 0, c->stream>>>(pa, sw);
-    else k_prep_realisation<false><<<n, 256, 0, c->stream>>>(pa, sw);
+    if (sw.fpp) k_prep_realisation<true><<<n, PREP_T, 0, c->stream>>>(pa, sw);
+    else k_prep_realisation<false><<<n, PREP_T, 0, c->stream>>>(pa, sw);
     prof_end(c);
     c->launches++;
     *h_true_out = h_true;

@@ -142,7 +142,7 @@ extern "C" int mmimo_mu_link_simulate(mmimo_ctx* c, const mmimo_mu_request* rq, 
             pa.n_ant = K; pa.n_frames = ni; pa.pa_kind = cfg.pa_kind; pa.is_mcnc = 1;
             pa.ibo_lin = mp.ibo_lin; pa.avg_symbol_power = mp.avg_symbol_power; pa.avg_sample_power = mp.avg_sample_power;
             pa.snr_lin = mp.snr_lin;
-            k_prep_realisation<false><<<ni, 256, 0, c->stream>>>(pa, SweepArgs{});
+            k_prep_realisation<false><<<ni, PREP_T, 0, c->stream>>>(pa, SweepArgs{});
             // With zero forcing the script's single-user arrays (n_users = 1) get their PA saturation power from the phase-only
             // precoder of antenna_array.py:175-178 (mean |v|^2 = 1: ibo * avg_sample_power) before McncReceiver.__init__
             // overwrites the precoder with MRT (corrector.py:135) - reproduced as written (tests/golden/mu_su_loop.npz)

@@ -284,43 +284,47 @@ __device__ __forceinline__ double block_sum_n(double v, double* red_s, int t) { 
     return s;
 }
 
+#ifndef PREP_T
+#define PREP_T 512  // threads per realisation CTA; N_SC / PREP_T sub-carrier slots per thread
+#endif
+constexpr int PREP_NS = N_SC / PREP_T, PREP_W = PREP_T / 32;
 template <bool SWEEP>
-__global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, const SweepArgs sw) {
-    __shared__ float part_s[MAX_ANT][8];
+__global__ void __launch_bounds__(PREP_T) k_prep_realisation(const PrepArgs a, const SweepArgs sw) {
+    __shared__ float part_s[MAX_ANT][PREP_W];
     __shared__ float alpha_s[MAX_ANT];
     __shared__ double vkpow_s[MAX_ANT];
-    __shared__ double red_s[8];
+    __shared__ double red_s[PREP_W];
     const int f = blockIdx.x, t = threadIdx.x, K = a.n_ant;
     const float2* __restrict__ H = a.h_loop + f * a.h_fs;
     const float2* __restrict__ Vin = a.v_in ? a.v_in + (size_t)f * K * N_SC : nullptr;
     float2* Vout = a.v_out ? a.v_out + (size_t)f * K * N_SC : nullptr;
 
-    float ninv[8];
+    float ninv[PREP_NS];
     if (!Vin && sw.sscale_ready) {
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) ninv[jp] = a.sscale[(size_t)f * N_SC + jp * 256 + t] * 64.0f;  // exact
+        for (int jp = 0; jp < PREP_NS; ++jp) ninv[jp] = a.sscale[(size_t)f * N_SC + jp * PREP_T + t] * 64.0f;  // exact
     } else if (!Vin) {
-        float nrm[8];
+        float nrm[PREP_NS];
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) nrm[jp] = 0.f;
+        for (int jp = 0; jp < PREP_NS; ++jp) nrm[jp] = 0.f;
         for (int k = 0; k < K; ++k) {
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) {
-                const float2 h = H[(size_t)k * N_SC + jp * 256 + t];
+            for (int jp = 0; jp < PREP_NS; ++jp) {
+                const float2 h = H[(size_t)k * N_SC + jp * PREP_T + t];
                 nrm[jp] = fmaf(h.x, h.x, fmaf(h.y, h.y, nrm[jp]));
             }
         }
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) ninv[jp] = 1.0f / sqrtf(nrm[jp]);
+        for (int jp = 0; jp < PREP_NS; ++jp) ninv[jp] = 1.0f / sqrtf(nrm[jp]);
     }
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) a.sscale[(size_t)f * N_SC + jp * 256 + t] = Vin ? 0.015625f : ninv[jp] * 0.015625f;
+    for (int jp = 0; jp < PREP_NS; ++jp) a.sscale[(size_t)f * N_SC + jp * PREP_T + t] = Vin ? 0.015625f : ninv[jp] * 0.015625f;
     // precoder out + per-antenna power
     for (int k = 0; k < K; ++k) {
         float pw = 0.f;
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
-            const int p = jp * 256 + t;
+        for (int jp = 0; jp < PREP_NS; ++jp) {
+            const int p = jp * PREP_T + t;
             float2 v;
             if (Vin) v = Vin[(size_t)k * N_SC + p];
             else {
@@ -338,7 +342,7 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
     if (t < K) {
         double s = 0.0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) s += (double)part_s[t][w];
+        for (int w = 0; w < PREP_W; ++w) s += (double)part_s[t][w];
         vkpow_s[t] = s;
         // mp_model.py:315-317 + modulation.py:178-189
         const double g2 = ((SWEEP && sw.ibo_lin_tab) ? sw.ibo_lin_tab[(sw.frame0 + (unsigned)f) / (unsigned)sw.fpp] : a.ibo_lin) * (double)N_SC / (s * (double)K);
@@ -349,14 +353,14 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
     }
     __syncthreads();
     // AGC vectors
-    float2 agc[8], hv[8];
+    float2 agc[PREP_NS], hv[PREP_NS];
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) agc[jp] = hv[jp] = make_float2(0.f, 0.f);
+    for (int jp = 0; jp < PREP_NS; ++jp) agc[jp] = hv[jp] = make_float2(0.f, 0.f);
     for (int k = 0; k < K; ++k) {
         const float al = alpha_s[k];
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
-            const int p = jp * 256 + t;
+        for (int jp = 0; jp < PREP_NS; ++jp) {
+            const int p = jp * PREP_T + t;
             const float2 h = H[(size_t)k * N_SC + p];
             float2 v;
             if (Vin) v = Vin[(size_t)k * N_SC + p];
@@ -368,8 +372,8 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
     }
     double s_agc = 0.0, s_hv = 0.0;
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) {
-        const int p = jp * 256 + t;
+    for (int jp = 0; jp < PREP_NS; ++jp) {
+        const int p = jp * PREP_T + t;
         const double a2 = (double)agc[jp].x * agc[jp].x + (double)agc[jp].y * agc[jp].y;
         const double h2 = (double)hv[jp].x * hv[jp].x + (double)hv[jp].y * hv[jp].y;
         s_agc += a2; s_hv += h2;
@@ -377,8 +381,8 @@ __global__ void __launch_bounds__(256) k_prep_realisation(const PrepArgs a, cons
         a.agc_inv[(size_t)f * N_SC + p] = make_float2((float)(agc[jp].x / (64.0 * a2)), (float)(-agc[jp].y / (64.0 * a2)));
         a.hkvk_inv[(size_t)f * N_SC + p] = make_float2((float)(hv[jp].x / h2), (float)(-hv[jp].y / h2));
     }
-    s_agc = block_sum_256(s_agc, red_s, t);
-    s_hv = block_sum_256(s_hv, red_s, t);
+    s_agc = block_sum_n<PREP_W>(s_agc, red_s, t);
+    s_hv = block_sum_n<PREP_W>(s_hv, red_s, t);
     if (t == 0) {
         double tot = 0.0;
         for (int k = 0; k < K; ++k) tot += vkpow_s[k];
@@ -634,51 +638,59 @@ struct CsiArgs {
 };
 
 // grid (K, F), or (1, F) with sscale_out: the CTA walks all antennas of the realisation and also writes the symbol scale
-__global__ void __launch_bounds__(256) k_csi_error(const CsiArgs a) {
-    __shared__ double red_s[8];
+#ifndef CSI_T
+#define CSI_T 256  // threads per CTA; N_SC / CSI_T slots per thread (512 measured slower: 2.33 vs 1.96 ms per 4144 realisations)
+#endif
+constexpr int CSI_NS = N_SC / CSI_T, CSI_W = CSI_T / 32;
+__global__ void __launch_bounds__(CSI_T) k_csi_error(const CsiArgs a) {
+    __shared__ double red_s[CSI_W];
     const int f = blockIdx.y, t = threadIdx.x;
+    // slot of this thread's element jp: (2 q + e) 256 + t' with t' = t mod 256, e = jp mod 2, q = t / 256 + (CSI_T / 256) (jp / 2):
+    // both halves of a Philox block (round 1: block 4 t' + q -> slots (2 q) 256 + t' and (2 q + 1) 256 + t') stay in one thread
+    auto slot = [&](const int jp) { return (2 * ((t >> 8) + (CSI_T / 256) * (jp >> 1)) + (jp & 1)) * 256 + (t & 255); };
     const int k0 = a.sscale_out ? 0 : blockIdx.x, k1 = a.sscale_out ? a.n_ant : blockIdx.x + 1;
     const uint64_t fid = a.frame_id0 + f;
-    float nrm[8];
+    float nrm[CSI_NS];
 #pragma unroll
-    for (int jp = 0; jp < 8; ++jp) nrm[jp] = 0.f;
+    for (int jp = 0; jp < CSI_NS; ++jp) nrm[jp] = 0.f;
     for (int k = k0; k < k1; ++k) {
         const float2* in = a.h_in + ((size_t)f * a.n_ant + k) * N_SC;
         float2* out = a.h_out + ((size_t)f * a.n_ant + k) * N_SC;
-        float2 h[8];
+        float2 h[CSI_NS];
         double pw = 0.0;
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
-            h[jp] = in[jp * 256 + t];
+        for (int jp = 0; jp < CSI_NS; ++jp) {
+            h[jp] = in[slot(jp)];
             pw += (double)h[jp].x * h[jp].x + (double)h[jp].y * h[jp].y;
         }
-        pw = block_sum_256(pw, red_s, t) / N_SC;
+        pw = block_sum_n<CSI_W>(pw, red_s, t) / N_SC;
         const float sig = a.eps * (float)sqrt(0.5 * pw);
-        float2 g[8];
+        float2 g[CSI_NS];
         if (a.noise_in) {
             const float2* nz = a.noise_in + ((size_t)f * a.n_ant + k) * N_SC;
 #pragma unroll
-            for (int jp = 0; jp < 8; ++jp) g[jp] = nz[jp * 256 + t];
+            for (int jp = 0; jp < CSI_NS; ++jp) g[jp] = nz[slot(jp)];
         } else {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int j2 = 0; j2 < CSI_NS / 2; ++j2) {
+                const int q = (t >> 8) + (CSI_T / 256) * j2;
                 uint32_t r[4];
-                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)(t * 4 + q),
+                philox4x32_10((uint32_t)fid, (uint32_t)(fid >> 32), a.stream + ((uint32_t)k << 8), (uint32_t)((t & 255) * 4 + q),
                               (uint32_t)a.seed, (uint32_t)(a.seed >> 32), r);
-                g[2 * q] = box_muller_fast(r[0], r[1]);
-                g[2 * q + 1] = box_muller_fast(r[2], r[3]);
+                g[2 * j2] = box_muller_fast(r[0], r[1]);
+                g[2 * j2 + 1] = box_muller_fast(r[2], r[3]);
             }
         }
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) {
+        for (int jp = 0; jp < CSI_NS; ++jp) {
             const float2 o = make_float2(fmaf(a.scale, h[jp].x, sig * g[jp].x), fmaf(a.scale, h[jp].y, sig * g[jp].y));
-            out[jp * 256 + t] = o;
+            out[slot(jp)] = o;
             nrm[jp] = fmaf(o.x, o.x, fmaf(o.y, o.y, nrm[jp]));  // operation order of k_prep_realisation's first pass
         }
     }
     if (a.sscale_out) {
 #pragma unroll
-        for (int jp = 0; jp < 8; ++jp) a.sscale_out[(size_t)f * N_SC + jp * 256 + t] = (1.0f / sqrtf(nrm[jp])) * 0.015625f;
+        for (int jp = 0; jp < CSI_NS; ++jp) a.sscale_out[(size_t)f * N_SC + slot(jp)] = (1.0f / sqrtf(nrm[jp])) * 0.015625f;
     }
 }
 
