@@ -5,6 +5,8 @@
   link_k64_los_mcnc32.npz   the headline shape (BASELINE configs[1]): K=64 LOS MRT, soft limiter IBO 0 dB, Eb/N0 15 dB,
                             MCNC iterations 0..5, 32 frames (same seeds as link_k64_los_mcnc: its 3 frames are the first 3)
   link_k64_los_cnc16.npz    the same link with the CNC receiver (configs[1] names CNC and MCNC), 16 frames, iterations 0,1,2,5
+  link_k64_two_path_mcnc8.npz, link_k64_rayleigh_mcnc8.npz   BASELINE configs[2] at its named size: K=64 two-path and Rayleigh
+                            channels, MCNC iterations 0..5, 8 frames each (python tests/golden/make_golden_k64.py chan)
   mu_k64.npz                two users, K=64, MU-MRT and ZF, McncMuReceiver per user (configs[4], the frame of
                             main_multiuser/main_multiuser_mcnc_ber_vs_ebn0.py:514-642); channels are NOT stored (2 x 4 MiB):
                             the users' positions are, and channel.MisoLosFd is pinned by link_oracle.channel_los elsewhere
@@ -106,5 +108,8 @@ if __name__ == "__main__":
         golden_mu_k64()
     if "cnc" in what:
         mg.golden_link("link_k64_los_cnc16", 64, "los", 0.0, 15.0, 16, [0, 1, 2, 5], [1, 2, 3], is_mcnc=False, full_frames=2)
+    if "chan" in what:
+        mg.golden_link("link_k64_two_path_mcnc8", 64, "two_path", 0.0, 15.0, 8, [0, 1, 2, 3, 4, 5], [11, 12, 13], full_frames=2)
+        mg.golden_link("link_k64_rayleigh_mcnc8", 64, "rayleigh", 0.0, 15.0, 8, [0, 1, 2, 3, 4, 5], [14, 15, 16], full_frames=2)
     if "mcnc" in what:
         mg.golden_link("link_k64_los_mcnc32", 64, "los", 0.0, 15.0, 32, [0, 1, 2, 3, 4, 5], [1, 2, 3], full_frames=3)

@@ -17,7 +17,7 @@ from test_gpu_dropin_blocks import M, build_objects, make_channel  # noqa: F401
 pytestmark = pytest.mark.gpu
 
 CASES = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k8_los_csi", "link_k8_los_rapp",
-         "link_k64_los_cnc16"]
+         "link_k64_los_cnc16", "link_k64_two_path_mcnc8", "link_k64_rayleigh_mcnc8"]
 
 
 def run_link(M, g, rng_mode="numpy", n_frames=None, bits_max=None, n_err_min=int(1e12), path="fused"):

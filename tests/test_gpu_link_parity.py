@@ -18,8 +18,10 @@ TOL = 1e-5      # relative L2, complex stages
 GOLDEN_4096 = ["link_k64_los_mcnc", "link_k8_two_path_mcnc_clean", "link_k4_rayleigh_cnc", "link_k8_los_csi",
                "link_k8_los_rapp",
                # the headline shape with 32 frames and its CNC twin with 16 (tests/golden/make_golden_k64.py)
-               "link_k64_los_mcnc32", "link_k64_los_cnc16"]
-# Frames that may hit a sub-margin decision, per case.  Measured on the B200 (profiles/r02_margin_histogram.json): of 1.35 M
+               "link_k64_los_mcnc32", "link_k64_los_cnc16",
+               # BASELINE configs[2] at its named size: K=64 two-path and Rayleigh channels, 8 frames each
+               "link_k64_two_path_mcnc8", "link_k64_rayleigh_mcnc8"]
+# Frames that may hit a sub-margin decision, per case.  Measured on the B200 (profiles/r02_margin_histogram.json): of 1.74 M
 # decisions compared over all cases NONE differed from the reference, although the oracle's slicer input came as close as
 # 5e-7 to a boundary; the allowance below is slack for other inputs, the rule itself (parity_util.check_frame: a differing
 # decision must sit within MARGIN of a boundary) is never relaxed.
