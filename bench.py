@@ -254,7 +254,7 @@ def secondary_workloads(eng, a, snr, peak):
                                  for k, b in zip(eng.STAGE_KERNELS, eng.STAGE_BYTES_PER_ROW)},
                      "note": "k_map_precode, k_fft4096_rows<+1>, k_pa<soft limiter>, k_fft4096_rows<-1>, k_propagate timed one by one "
                              "with CUDA events (mmimo_measure_stage_kernels); one stage call of the drop-in classes (64 rows, host "
-                             "buffers) is latency-bound, this is the kernels' own rate"}
+                             "buffers) is latency-bound, this is the kernels' own rate; the peak is a measured COPY bandwidth (torch b.copy_(a)), not a hard ceiling: a streaming kernel with 16-byte accesses can exceed it by a few per cent (ncu DRAM peak of this GPU: 8.18 TB/s)"}
     return out
 
 
