@@ -170,7 +170,8 @@ class AntennaArray(ABC):
                 if not default_one:
                     raise TypeError("precoding matrix is not set")
                 continue
-            a = np.abs(np.asarray(p)) ** 2
+            p = np.asarray(p)
+            a = p.real * p.real + p.imag * p.imag  # |v|^2 without the square root of np.abs
             pw[k, :] = a if a.ndim == 1 else np.sum(a, axis=0)
         return pw
 
@@ -178,12 +179,15 @@ class AntennaArray(ABC):
         """Set IBO / TOI, Bussgang alpha and the precoding-aware average sample power of every element
         (antenna_array.py:313-360)."""
         avg_precoding_gain = np.average(self._precoding_power_per_antenna(default_one=True))
+        alpha = None  # calc_alpha depends on ibo_db only: evaluated once, not once per antenna
         for tx in self.array_elements:
             if isinstance(tx.impairment, distortion.ThirdOrderNonLin):
                 tx.modem.alpha = alpha_val
                 tx.impairment.set_toi(ibo_db)
             else:
-                tx.modem.alpha = tx.modem.calc_alpha(ibo_db=ibo_db)
+                if alpha is None:
+                    alpha = tx.modem.calc_alpha(ibo_db=ibo_db)
+                tx.modem.alpha = alpha
                 tx.impairment.set_ibo(ibo_db)
             tx.impairment.set_avg_sample_power(avg_sample_pow * avg_precoding_gain)
 
